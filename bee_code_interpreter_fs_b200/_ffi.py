@@ -1,0 +1,70 @@
+"""ctypes binding of include/b200cas.h.  No fallback: a missing library is an error."""
+from __future__ import annotations
+
+import ctypes
+import os
+
+from ._build import LIB_PATH
+
+CAS_OK = 0
+CAS_E_CUDA, CAS_E_ARG, CAS_E_NOMEM, CAS_E_NODEVICE = -1, -2, -3, -4
+OPT_KERNEL, OPT_FMA_LEVEL, OPT_WAVE_BYTES, OPT_PACK_THREADS, OPT_CTAS_PER_SM = 1, 2, 3, 4, 5
+
+# Every symbol include/b200cas.h declares (tests check the library exports them all).
+SYMBOLS = (
+    "cas_create", "cas_destroy", "cas_last_error", "cas_set_option", "cas_get_option", "cas_device_info",
+    "cas_hash_host", "cas_hash_device", "cas_hash_device_uniform", "cas_gen_synthetic", "cas_int32_peak",
+    "cas_launch_count", "cas_version",
+)
+
+
+class CasError(RuntimeError):
+    """The engine reported a failure; never swallowed into a placeholder digest."""
+
+    def __init__(self, code: int, message: str):
+        super().__init__(f"b200cas error {code}: {message}")
+        self.code = code
+
+
+_lib = None
+
+
+def load() -> ctypes.CDLL:
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(nvcc, sm_100a). This engine has no CPU fallback."
+        )
+    lib = ctypes.CDLL(LIB_PATH)
+    vp, u64, i64, ci = ctypes.c_void_p, ctypes.c_uint64, ctypes.c_int64, ctypes.c_int
+    lib.cas_create.argtypes = [ci, ctypes.POINTER(vp)]
+    lib.cas_create.restype = ci
+    lib.cas_destroy.argtypes = [vp]
+    lib.cas_destroy.restype = None
+    lib.cas_last_error.argtypes = [vp]
+    lib.cas_last_error.restype = ctypes.c_char_p
+    lib.cas_set_option.argtypes = [vp, ci, i64]
+    lib.cas_set_option.restype = ci
+    lib.cas_get_option.argtypes = [vp, ci, ctypes.POINTER(i64)]
+    lib.cas_get_option.restype = ci
+    lib.cas_device_info.argtypes = [vp, ctypes.POINTER(ci), ctypes.POINTER(ci), ctypes.POINTER(u64)]
+    lib.cas_device_info.restype = ci
+    lib.cas_hash_host.argtypes = [vp, vp, vp, vp, u64, vp]
+    lib.cas_hash_host.restype = ci
+    lib.cas_hash_device.argtypes = [vp, vp, vp, vp, vp, u64, vp, vp]
+    lib.cas_hash_device.restype = ci
+    lib.cas_hash_device_uniform.argtypes = [vp, vp, u64, u64, u64, vp, vp]
+    lib.cas_hash_device_uniform.restype = ci
+    lib.cas_gen_synthetic.argtypes = [vp, vp, u64, u64, u64, u64, u64, vp]
+    lib.cas_gen_synthetic.restype = ci
+    lib.cas_int32_peak.argtypes = [vp, ci, ci, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double)]
+    lib.cas_int32_peak.restype = ci
+    lib.cas_launch_count.argtypes = [vp]
+    lib.cas_launch_count.restype = u64
+    lib.cas_version.argtypes = []
+    lib.cas_version.restype = ctypes.c_char_p
+    _lib = lib
+    return lib

@@ -1,0 +1,656 @@
+// C ABI of the B200 SHA-256 content-addressing engine (see include/b200cas.h).
+//
+// Host side of the path that the reference leaves to Storage.writer/Storage.write
+// (/root/reference/src/code_interpreter/services/storage.py:44-63): take a batch
+// of objects, return their SHA-256 object ids.  Device side: csrc/sha256_batch.cuh.
+//
+// Host-buffer pipeline (cas_hash_host): objects are ordered longest-first, cut
+// into waves, packed 16-byte aligned into pinned staging by a few host threads
+// (or DMA'd straight from the caller's memory when that is pinned and laid out
+// contiguously), copied with cudaMemcpyAsync on a copy stream while the previous
+// wave is hashed on a compute stream; 32-byte digests come back per wave.
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <atomic>
+#include <condition_variable>
+#include <functional>
+#include <mutex>
+#include <numeric>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "../../include/b200cas.h"
+#include "peak.cuh"
+#include "sha256_batch.cuh"
+#include "synth.cuh"
+
+namespace {
+
+constexpr int NBUF = 3;
+constexpr uint64_t MiB = 1ull << 20;
+
+std::string g_create_error;
+
+// Small fork-join pool for packing objects into pinned staging.
+class PackPool {
+public:
+    explicit PackPool(int n) : stop_(false), gen_(0), pending_(0) {
+        for (int i = 0; i < n; ++i) th_.emplace_back([this, i] { loop(i); });
+    }
+    ~PackPool() {
+        {
+            std::lock_guard<std::mutex> lk(m_);
+            stop_ = true;
+            ++gen_;
+        }
+        cv_.notify_all();
+        for (auto& t : th_) t.join();
+    }
+    int size() const { return (int)th_.size(); }
+    // Runs fn(worker_index) on every worker and waits for all of them.
+    void run(const std::function<void(int)>& fn) {
+        std::unique_lock<std::mutex> lk(m_);
+        fn_ = &fn;
+        pending_ = (int)th_.size();
+        ++gen_;
+        cv_.notify_all();
+        done_.wait(lk, [this] { return pending_ == 0; });
+        fn_ = nullptr;
+    }
+
+private:
+    void loop(int idx) {
+        uint64_t seen = 0;
+        for (;;) {
+            const std::function<void(int)>* fn;
+            {
+                std::unique_lock<std::mutex> lk(m_);
+                cv_.wait(lk, [&] { return gen_ != seen; });
+                seen = gen_;
+                if (stop_) return;
+                fn = fn_;
+            }
+            (*fn)(idx);
+            {
+                std::lock_guard<std::mutex> lk(m_);
+                if (--pending_ == 0) done_.notify_all();
+            }
+        }
+    }
+    std::vector<std::thread> th_;
+    std::mutex m_;
+    std::condition_variable cv_, done_;
+    const std::function<void(int)>* fn_ = nullptr;
+    bool stop_;
+    uint64_t gen_;
+    int pending_;
+};
+
+struct WaveBuf {
+    uint8_t* h_stage = nullptr;  // pinned, data_cap bytes
+    uint8_t* d_data = nullptr;   // device, data_cap bytes
+    uint64_t data_cap = 0;
+    uint64_t* h_meta = nullptr;  // pinned, 2*obj_cap words: offsets then lengths
+    uint64_t* d_meta = nullptr;
+    uint8_t* h_dig = nullptr;    // pinned, 32*obj_cap
+    uint8_t* d_dig = nullptr;
+    uint64_t obj_cap = 0;
+    cudaEvent_t ev_done = nullptr;
+    bool busy = false;
+    uint64_t first = 0, count = 0;  // slice of the schedule this buffer holds
+};
+
+}  // namespace
+
+struct cas_ctx {
+    int device = 0;
+    int sm_count = 0;
+    int clock_khz = 0;
+    uint64_t mem_bytes = 0;
+    std::string err;
+    int kernel = 2;
+    int fma_level = 3;
+    int ctas_per_sm = 4;
+    void* encode_tiled = nullptr;  // cuTensorMapEncodeTiled, resolved through the runtime
+    uint64_t wave_bytes = 256 * MiB;
+    int pack_threads = 0;
+    uint64_t launches = 0;
+    cudaStream_t s_copy = nullptr, s_comp = nullptr;
+    cudaEvent_t ev_h2d[NBUF] = {nullptr, nullptr, nullptr};
+    WaveBuf buf[NBUF];
+    PackPool* pool = nullptr;
+    uint32_t* d_sink = nullptr;
+};
+
+namespace {
+
+int fail(cas_ctx* c, int code, const char* what, cudaError_t e = cudaSuccess) {
+    char msg[512];
+    if (e != cudaSuccess)
+        snprintf(msg, sizeof msg, "%s: %s (%s)", what, cudaGetErrorName(e), cudaGetErrorString(e));
+    else
+        snprintf(msg, sizeof msg, "%s", what);
+    if (c) c->err = msg; else g_create_error = msg;
+    return code;
+}
+
+#define CU(call)                                                   \
+    do {                                                           \
+        cudaError_t e_ = (call);                                   \
+        if (e_ != cudaSuccess) return fail(ctx, CAS_E_CUDA, #call, e_); \
+    } while (0)
+
+constexpr int THREADS = 256;
+
+// cuTensorMapEncodeTiled is a driver-API entry point; it is looked up through the
+// runtime so that the library has no link-time dependency on libcuda.
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+bool tma_eligible(const cas::BatchArgs& a) {
+    return a.off == nullptr && a.order == nullptr && a.ulen >= 64 && a.ulen < (1ull << 31) && a.n < (1ull << 31) &&
+           (a.stride % 16) == 0 && a.stride < (1ull << 40) && (((uintptr_t)a.base) % 16) == 0;
+}
+
+template <typename K>
+cudaError_t configure_smem(K k, int smem, bool (&done)[16]) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 16 && done[dev]) return cudaSuccess;
+    cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(k, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    if (e != cudaSuccess) return e;
+    if (dev < 16) done[dev] = true;
+    return cudaSuccess;
+}
+
+template <int FMA, int MIN_CTAS>
+cudaError_t launch_one(cas_ctx* ctx, int kernel, const cas::BatchArgs& a, cudaStream_t st) {
+    constexpr int NSTAGE = 2;
+    const unsigned grid = (unsigned)((a.n + THREADS - 1) / THREADS);
+    if (kernel == 2 && tma_eligible(a)) {
+        CUtensorMap tm;
+        const cuuint64_t gdim[2] = {(cuuint64_t)a.ulen, (cuuint64_t)a.n};
+        const cuuint64_t gstride[1] = {(cuuint64_t)a.stride};
+        const cuuint32_t box[2] = {64u, 32u};
+        const cuuint32_t estr[2] = {1u, 1u};
+        CUresult r = reinterpret_cast<EncodeTiledFn>(ctx->encode_tiled)(
+            &tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<uint8_t*>(a.base), gdim, gstride, box, estr,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) return cudaErrorInvalidValue;
+        cas::TensorMapBlob blob;
+        static_assert(sizeof(blob) == sizeof(tm), "CUtensorMap is 128 bytes");
+        memcpy(&blob, &tm, sizeof tm);
+        constexpr int smem = cas::tma_smem_bytes<NSTAGE, THREADS>();
+        auto k = cas::kernel_tma<FMA, NSTAGE, THREADS, MIN_CTAS>;
+        static bool done[16] = {};
+        cudaError_t e = configure_smem(k, smem, done);
+        if (e != cudaSuccess) return e;
+        k<<<grid, THREADS, smem, st>>>(blob, a);
+    } else if (kernel == 1) {
+        constexpr int smem = cas::bulk_smem_bytes<NSTAGE, THREADS>();
+        auto k = cas::kernel_bulk<FMA, NSTAGE, THREADS, MIN_CTAS>;
+        static bool done[16] = {};
+        cudaError_t e = configure_smem(k, smem, done);
+        if (e != cudaSuccess) return e;
+        k<<<grid, THREADS, smem, st>>>(a);
+    } else {
+        cas::kernel_ldg<FMA, THREADS, MIN_CTAS><<<grid, THREADS, 0, st>>>(a);
+    }
+    return cudaGetLastError();
+}
+
+template <int FMA>
+cudaError_t launch_occ(cas_ctx* ctx, int kernel, const cas::BatchArgs& a, cudaStream_t st) {
+    switch (ctx->ctas_per_sm) {
+        case 2: return launch_one<FMA, 2>(ctx, kernel, a, st);
+        case 3: return launch_one<FMA, 3>(ctx, kernel, a, st);
+        default: return launch_one<FMA, 4>(ctx, kernel, a, st);
+    }
+}
+
+int launch_batch(cas_ctx* ctx, cas::BatchArgs a, cudaStream_t st) {
+    if (a.n == 0) return CAS_OK;
+    if (a.n > (1ull << 36)) return fail(ctx, CAS_E_ARG, "too many objects in one launch");
+    a.one = 1u;
+    a.zero = 0u;
+    cudaError_t e;
+    switch (ctx->fma_level) {
+        case 0: e = launch_occ<0>(ctx, ctx->kernel, a, st); break;
+        case 1: e = launch_occ<1>(ctx, ctx->kernel, a, st); break;
+        case 2: e = launch_occ<2>(ctx, ctx->kernel, a, st); break;
+        default: e = launch_occ<3>(ctx, ctx->kernel, a, st); break;
+    }
+    if (e != cudaSuccess) return fail(ctx, CAS_E_CUDA, "sha256 batch kernel launch", e);
+    ++ctx->launches;
+    return CAS_OK;
+}
+
+inline uint64_t align16(uint64_t x) { return (x + 15u) & ~15ull; }
+inline uint64_t nblocks(uint64_t len) { return (len + 9 + 63) / 64; }
+
+void free_buf(WaveBuf& b) {
+    if (b.h_stage) cudaFreeHost(b.h_stage);
+    if (b.d_data) cudaFree(b.d_data);
+    if (b.h_meta) cudaFreeHost(b.h_meta);
+    if (b.d_meta) cudaFree(b.d_meta);
+    if (b.h_dig) cudaFreeHost(b.h_dig);
+    if (b.d_dig) cudaFree(b.d_dig);
+    if (b.ev_done) cudaEventDestroy(b.ev_done);
+    b = WaveBuf();
+}
+
+int ensure_buf(cas_ctx* ctx, WaveBuf& b, uint64_t data_bytes, uint64_t objs) {
+    if (!b.ev_done) CU(cudaEventCreateWithFlags(&b.ev_done, cudaEventDisableTiming));
+    if (data_bytes > b.data_cap) {
+        if (b.h_stage) cudaFreeHost(b.h_stage);
+        if (b.d_data) cudaFree(b.d_data);
+        b.h_stage = nullptr; b.d_data = nullptr; b.data_cap = 0;
+        const uint64_t cap = (data_bytes + MiB - 1) & ~(MiB - 1);
+        if (cudaHostAlloc((void**)&b.h_stage, cap, cudaHostAllocDefault) != cudaSuccess) {
+            cudaGetLastError();
+            return fail(ctx, CAS_E_NOMEM, "pinned staging allocation failed");
+        }
+        if (cudaMalloc((void**)&b.d_data, cap) != cudaSuccess) {
+            cudaGetLastError();
+            return fail(ctx, CAS_E_NOMEM, "device wave buffer allocation failed");
+        }
+        b.data_cap = cap;
+    }
+    if (objs > b.obj_cap) {
+        if (b.h_meta) cudaFreeHost(b.h_meta);
+        if (b.d_meta) cudaFree(b.d_meta);
+        if (b.h_dig) cudaFreeHost(b.h_dig);
+        if (b.d_dig) cudaFree(b.d_dig);
+        b.h_meta = nullptr; b.d_meta = nullptr; b.h_dig = nullptr; b.d_dig = nullptr; b.obj_cap = 0;
+        const uint64_t cap = std::max<uint64_t>(1024, objs + objs / 4);
+        if (cudaHostAlloc((void**)&b.h_meta, cap * 16, cudaHostAllocDefault) != cudaSuccess ||
+            cudaHostAlloc((void**)&b.h_dig, cap * 32, cudaHostAllocDefault) != cudaSuccess) {
+            cudaGetLastError();
+            return fail(ctx, CAS_E_NOMEM, "pinned metadata allocation failed");
+        }
+        if (cudaMalloc((void**)&b.d_meta, cap * 16) != cudaSuccess ||
+            cudaMalloc((void**)&b.d_dig, cap * 32) != cudaSuccess) {
+            cudaGetLastError();
+            return fail(ctx, CAS_E_NOMEM, "device metadata allocation failed");
+        }
+        b.obj_cap = cap;
+    }
+    return CAS_OK;
+}
+
+int ensure_streams(cas_ctx* ctx) {
+    if (!ctx->s_copy) CU(cudaStreamCreateWithFlags(&ctx->s_copy, cudaStreamNonBlocking));
+    if (!ctx->s_comp) CU(cudaStreamCreateWithFlags(&ctx->s_comp, cudaStreamNonBlocking));
+    for (int i = 0; i < NBUF; ++i)
+        if (!ctx->ev_h2d[i]) CU(cudaEventCreateWithFlags(&ctx->ev_h2d[i], cudaEventDisableTiming));
+    if (!ctx->pool) {
+        int n = ctx->pack_threads;
+        if (n <= 0) {
+            n = (int)std::thread::hardware_concurrency();
+            n = std::max(1, std::min(n, 16));
+        }
+        ctx->pool = new PackPool(n);
+    }
+    return CAS_OK;
+}
+
+bool host_ptr_is_pinned(const void* p) {
+    if (!p) return false;
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return at.type == cudaMemoryTypeHost;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* cas_version(void) { return "b200cas 0.1 sm_100a"; }
+
+const char* cas_last_error(const cas_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+int cas_create(int device, cas_ctx** out) {
+    if (!out) return fail(nullptr, CAS_E_ARG, "cas_create: out is NULL");
+    *out = nullptr;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return fail(nullptr, CAS_E_NODEVICE, "cas_create: no CUDA device is visible (this engine has no CPU fallback)", e);
+    }
+    if (device < 0 || device >= ndev) return fail(nullptr, CAS_E_ARG, "cas_create: device index out of range");
+    cudaDeviceProp prop;
+    if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess)
+        return fail(nullptr, CAS_E_CUDA, "cudaGetDeviceProperties", e);
+    if (prop.major != 10) {
+        char msg[160];
+        snprintf(msg, sizeof msg, "cas_create: device %d is sm_%d%d; this library carries sm_100a code only", device,
+                 prop.major, prop.minor);
+        return fail(nullptr, CAS_E_NODEVICE, msg);
+    }
+    if ((e = cudaSetDevice(device)) != cudaSuccess) return fail(nullptr, CAS_E_CUDA, "cudaSetDevice", e);
+    cas_ctx* ctx = new (std::nothrow) cas_ctx();
+    if (!ctx) return fail(nullptr, CAS_E_NOMEM, "cas_create: out of host memory");
+    ctx->device = device;
+    ctx->sm_count = prop.multiProcessorCount;
+    int khz = 0;
+    cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, device);
+    ctx->clock_khz = khz;
+    ctx->mem_bytes = prop.totalGlobalMem;
+    cudaDriverEntryPointQueryResult qres;
+    e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ctx->encode_tiled, cudaEnableDefault, &qres);
+    if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !ctx->encode_tiled) {
+        delete ctx;
+        return fail(nullptr, CAS_E_CUDA, "cuTensorMapEncodeTiled not available from this driver", e);
+    }
+    if (const char* v = getenv("B200CAS_KERNEL")) ctx->kernel = std::max(0, std::min(2, atoi(v)));
+    if (const char* v = getenv("B200CAS_FMA")) ctx->fma_level = std::max(0, std::min(3, atoi(v)));
+    if (const char* v = getenv("B200CAS_CTAS")) ctx->ctas_per_sm = std::max(2, std::min(4, atoi(v)));
+    *out = ctx;
+    return CAS_OK;
+}
+
+void cas_destroy(cas_ctx* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    if (ctx->s_comp) cudaStreamSynchronize(ctx->s_comp);
+    if (ctx->s_copy) cudaStreamSynchronize(ctx->s_copy);
+    for (auto& b : ctx->buf) free_buf(b);
+    for (auto& ev : ctx->ev_h2d)
+        if (ev) cudaEventDestroy(ev);
+    if (ctx->s_comp) cudaStreamDestroy(ctx->s_comp);
+    if (ctx->s_copy) cudaStreamDestroy(ctx->s_copy);
+    if (ctx->d_sink) cudaFree(ctx->d_sink);
+    delete ctx->pool;
+    delete ctx;
+}
+
+int cas_set_option(cas_ctx* ctx, int key, int64_t v) {
+    if (!ctx) return CAS_E_ARG;
+    switch (key) {
+        case CAS_OPT_KERNEL:
+            if (v < 0 || v > 2) return fail(ctx, CAS_E_ARG, "CAS_OPT_KERNEL must be 0, 1 or 2");
+            ctx->kernel = (int)v;
+            return CAS_OK;
+        case CAS_OPT_FMA_LEVEL:
+            if (v < 0 || v > 3) return fail(ctx, CAS_E_ARG, "CAS_OPT_FMA_LEVEL must be 0..3");
+            ctx->fma_level = (int)v;
+            return CAS_OK;
+        case CAS_OPT_WAVE_BYTES:
+            if (v < (int64_t)MiB) return fail(ctx, CAS_E_ARG, "CAS_OPT_WAVE_BYTES must be >= 1 MiB");
+            ctx->wave_bytes = ((uint64_t)v + MiB - 1) & ~(MiB - 1);
+            return CAS_OK;
+        case CAS_OPT_PACK_THREADS:
+            if (v < 1 || v > 256) return fail(ctx, CAS_E_ARG, "CAS_OPT_PACK_THREADS must be 1..256");
+            if (ctx->pool && ctx->pool->size() != (int)v) {
+                delete ctx->pool;
+                ctx->pool = nullptr;
+            }
+            ctx->pack_threads = (int)v;
+            return CAS_OK;
+        case CAS_OPT_CTAS_PER_SM:
+            if (v < 2 || v > 4) return fail(ctx, CAS_E_ARG, "CAS_OPT_CTAS_PER_SM must be 2, 3 or 4");
+            ctx->ctas_per_sm = (int)v;
+            return CAS_OK;
+    }
+    return fail(ctx, CAS_E_ARG, "unknown option key");
+}
+
+int cas_get_option(const cas_ctx* ctx, int key, int64_t* v) {
+    if (!ctx || !v) return CAS_E_ARG;
+    switch (key) {
+        case CAS_OPT_KERNEL: *v = ctx->kernel; return CAS_OK;
+        case CAS_OPT_FMA_LEVEL: *v = ctx->fma_level; return CAS_OK;
+        case CAS_OPT_WAVE_BYTES: *v = (int64_t)ctx->wave_bytes; return CAS_OK;
+        case CAS_OPT_PACK_THREADS: *v = ctx->pool ? ctx->pool->size() : ctx->pack_threads; return CAS_OK;
+        case CAS_OPT_CTAS_PER_SM: *v = ctx->ctas_per_sm; return CAS_OK;
+    }
+    return CAS_E_ARG;
+}
+
+int cas_device_info(const cas_ctx* ctx, int* sm_count, int* sm_clock_khz, uint64_t* mem_bytes) {
+    if (!ctx) return CAS_E_ARG;
+    if (sm_count) *sm_count = ctx->sm_count;
+    if (sm_clock_khz) *sm_clock_khz = ctx->clock_khz;
+    if (mem_bytes) *mem_bytes = ctx->mem_bytes;
+    return CAS_OK;
+}
+
+uint64_t cas_launch_count(const cas_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+int cas_hash_device(cas_ctx* ctx, const void* d_base, const uint64_t* d_off, const uint64_t* d_len,
+                    const uint32_t* d_order, uint64_t n, void* d_out, void* stream) {
+    if (!ctx) return CAS_E_ARG;
+    if (n == 0) return CAS_OK;
+    if (!d_off || !d_len || !d_out) return fail(ctx, CAS_E_ARG, "cas_hash_device: NULL offset/length/output array");
+    CU(cudaSetDevice(ctx->device));
+    cas::BatchArgs a{};
+    a.base = static_cast<const uint8_t*>(d_base);
+    a.off = d_off;
+    a.len = d_len;
+    a.order = d_order;
+    a.n = n;
+    a.out = static_cast<uint8_t*>(d_out);
+    return launch_batch(ctx, a, static_cast<cudaStream_t>(stream));
+}
+
+int cas_hash_device_uniform(cas_ctx* ctx, const void* d_base, uint64_t stride, uint64_t len, uint64_t n,
+                            void* d_out, void* stream) {
+    if (!ctx) return CAS_E_ARG;
+    if (n == 0) return CAS_OK;
+    if (!d_out || (!d_base && len)) return fail(ctx, CAS_E_ARG, "cas_hash_device_uniform: NULL buffer");
+    if (stride < len && n > 1) return fail(ctx, CAS_E_ARG, "cas_hash_device_uniform: stride smaller than length");
+    CU(cudaSetDevice(ctx->device));
+    cas::BatchArgs a{};
+    a.base = static_cast<const uint8_t*>(d_base);
+    a.stride = stride;
+    a.ulen = len;
+    a.n = n;
+    a.out = static_cast<uint8_t*>(d_out);
+    return launch_batch(ctx, a, static_cast<cudaStream_t>(stream));
+}
+
+int cas_gen_synthetic(cas_ctx* ctx, void* d_dst, uint64_t seed, uint64_t first_obj, uint64_t n, uint64_t len,
+                      uint64_t stride, void* stream) {
+    if (!ctx) return CAS_E_ARG;
+    if (n == 0 || len == 0) return CAS_OK;
+    if (!d_dst) return fail(ctx, CAS_E_ARG, "cas_gen_synthetic: NULL destination");
+    if (stride < len && n > 1) return fail(ctx, CAS_E_ARG, "cas_gen_synthetic: stride smaller than length");
+    CU(cudaSetDevice(ctx->device));
+    const uint64_t segs = (len + cas::SYNTH_SEG - 1) / cas::SYNTH_SEG;
+    // Launch in slices so that the 1-D grid stays below 2^31 CTAs.
+    const uint64_t max_objs = std::max<uint64_t>(1, ((1ull << 31) - 1) / segs);
+    for (uint64_t done = 0; done < n; done += max_objs) {
+        const uint64_t m = std::min(max_objs, n - done);
+        cas::kernel_synth<<<(unsigned)(m * segs), cas::SYNTH_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
+            static_cast<uint8_t*>(d_dst) + done * stride, seed, first_obj + done, m, len, stride, segs);
+        CU(cudaGetLastError());
+        ++ctx->launches;
+    }
+    return CAS_OK;
+}
+
+int cas_int32_peak(cas_ctx* ctx, int mode, int steps, double* lane_ops_per_s, double* ms_out) {
+    if (!ctx) return CAS_E_ARG;
+    if (mode < 0 || mode > 4 || steps < cas::PEAK_UNROLL) return fail(ctx, CAS_E_ARG, "cas_int32_peak: bad mode/steps");
+    CU(cudaSetDevice(ctx->device));
+    if (!ctx->d_sink) CU(cudaMalloc((void**)&ctx->d_sink, 256));
+    steps -= steps % cas::PEAK_UNROLL;
+    const unsigned grid = (unsigned)ctx->sm_count * 8u;
+    cudaEvent_t e0, e1;
+    CU(cudaEventCreate(&e0));
+    CU(cudaEventCreate(&e1));
+    float best = 0.f;
+    for (int rep = 0; rep < 3; ++rep) {  // first repetition is the warm-up
+        CU(cudaEventRecord(e0, 0));
+        switch (mode) {
+            case 0: cas::kernel_peak<0><<<grid, cas::PEAK_THREADS>>>(ctx->d_sink, steps, 1u, 12345u + rep); break;
+            case 1: cas::kernel_peak<1><<<grid, cas::PEAK_THREADS>>>(ctx->d_sink, steps, 1u, 12345u + rep); break;
+            case 2: cas::kernel_peak<2><<<grid, cas::PEAK_THREADS>>>(ctx->d_sink, steps, 1u, 12345u + rep); break;
+            case 3: cas::kernel_peak<3><<<grid, cas::PEAK_THREADS>>>(ctx->d_sink, steps, 1u, 12345u + rep); break;
+            default: cas::kernel_peak<4><<<grid, cas::PEAK_THREADS>>>(ctx->d_sink, steps, 1u, 12345u + rep); break;
+        }
+        CU(cudaGetLastError());
+        CU(cudaEventRecord(e1, 0));
+        CU(cudaEventSynchronize(e1));
+        float ms = 0.f;
+        CU(cudaEventElapsedTime(&ms, e0, e1));
+        ++ctx->launches;
+        if (rep > 0 && (best == 0.f || ms < best)) best = ms;
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    const double ops = (double)grid * cas::PEAK_THREADS * (double)steps * cas::peak_ops_per_step(mode);
+    if (lane_ops_per_s) *lane_ops_per_s = ops / (best * 1e-3);
+    if (ms_out) *ms_out = best;
+    return CAS_OK;
+}
+
+int cas_hash_host(cas_ctx* ctx, const void* base, const uint64_t* off, const uint64_t* len, uint64_t n,
+                  void* out32n) {
+    if (!ctx) return CAS_E_ARG;
+    if (n == 0) return CAS_OK;
+    if (!off || !len || !out32n) return fail(ctx, CAS_E_ARG, "cas_hash_host: NULL offset/length/output array");
+    if (n > 0xFFFFFFFFull) return fail(ctx, CAS_E_ARG, "cas_hash_host: more than 2^32-1 objects in one call");
+    CU(cudaSetDevice(ctx->device));
+    int rc = ensure_streams(ctx);
+    if (rc) return rc;
+    const uint8_t* hbase = static_cast<const uint8_t*>(base);
+    uint8_t* out = static_cast<uint8_t*>(out32n);
+    // A previous call that failed half-way may have left waves in flight.
+    for (auto& b : ctx->buf)
+        if (b.busy) {
+            cudaEventSynchronize(b.ev_done);
+            b.busy = false;
+        }
+
+    // Schedule: longest first when lengths differ, so that the 32 lanes of a warp
+    // carry messages of (nearly) equal block counts and big objects start early.
+    uint64_t total = 0, maxlen = 0;
+    bool uniform = true;
+    for (uint64_t i = 0; i < n; ++i) {
+        total += align16(len[i]);
+        maxlen = std::max(maxlen, len[i]);
+        uniform = uniform && len[i] == len[0];
+    }
+    std::vector<uint32_t> order(n);
+    std::iota(order.begin(), order.end(), 0u);
+    if (!uniform)
+        std::stable_sort(order.begin(), order.end(),
+                         [&](uint32_t a, uint32_t b) { return nblocks(len[a]) > nblocks(len[b]); });
+
+    // Wave size: small batches are cut finer so that copy and hash still overlap.
+    uint64_t wave_cap = std::min<uint64_t>(ctx->wave_bytes, std::max<uint64_t>(8 * MiB, (total / 8 + MiB - 1) & ~(MiB - 1)));
+    wave_cap = std::max<uint64_t>(wave_cap, align16(maxlen));
+    const uint64_t wave_objs = 1ull << 22;
+    const bool pinned_src = host_ptr_is_pinned(hbase);
+
+    auto drain = [&](WaveBuf& b) -> int {
+        if (!b.busy) return CAS_OK;
+        CU(cudaEventSynchronize(b.ev_done));
+        for (uint64_t k = 0; k < b.count; ++k) memcpy(out + 32ull * order[b.first + k], b.h_dig + 32ull * k, 32);
+        b.busy = false;
+        return CAS_OK;
+    };
+
+    uint64_t pos = 0;
+    int w = 0;
+    while (pos < n) {
+        // Cut the next wave.
+        uint64_t cnt = 0, bytes = 0;
+        while (pos + cnt < n && cnt < wave_objs) {
+            const uint64_t need = align16(len[order[pos + cnt]]);
+            if (cnt && bytes + need > wave_cap) break;
+            bytes += need;
+            ++cnt;
+        }
+        WaveBuf& b = ctx->buf[w % NBUF];
+        if ((rc = drain(b))) return rc;
+        if ((rc = ensure_buf(ctx, b, std::max<uint64_t>(bytes, 16), cnt))) return rc;
+        b.first = pos;
+        b.count = cnt;
+        uint64_t* h_off = b.h_meta;
+        uint64_t* h_len = b.h_meta + cnt;
+        uint64_t cursor = 0;
+        for (uint64_t k = 0; k < cnt; ++k) {
+            const uint64_t L = len[order[pos + k]];
+            h_off[k] = cursor;
+            h_len[k] = L;
+            cursor += align16(L);
+        }
+        // Direct DMA from the caller's pinned memory when the wave is a few
+        // contiguous runs whose objects all stay 16-byte aligned; else pack.
+        bool direct = false;
+        std::vector<std::pair<uint64_t, uint64_t>> runs;  // (first k, byte count)
+        if (pinned_src) {
+            direct = true;
+            uint64_t k = 0;
+            while (k < cnt && direct) {
+                uint64_t k0 = k, run_bytes = align16(len[order[pos + k]]);
+                const uint64_t src0 = off[order[pos + k]];
+                ++k;
+                while (k < cnt && off[order[pos + k]] == src0 + run_bytes) {
+                    run_bytes += align16(len[order[pos + k]]);
+                    ++k;
+                }
+                // The last object of a run may be shorter than its aligned slot.
+                const uint64_t last = order[pos + k - 1];
+                runs.emplace_back(k0, run_bytes - (align16(len[last]) - len[last]));
+                if (runs.size() > 64) direct = false;
+            }
+        }
+        if (direct) {
+            for (auto& r : runs)
+                if (r.second)
+                    CU(cudaMemcpyAsync(b.d_data + h_off[r.first], hbase + off[order[pos + r.first]], r.second,
+                                       cudaMemcpyHostToDevice, ctx->s_copy));
+        } else {
+            const int T = ctx->pool->size();
+            const uint64_t share = (bytes + T - 1) / (uint64_t)T;
+            ctx->pool->run([&](int t) {
+                const uint64_t lo = share * (uint64_t)t, hi = std::min(bytes, lo + share);
+                if (lo >= hi) return;
+                // first object whose slot starts at or after lo
+                uint64_t k = std::lower_bound(h_off, h_off + cnt, lo) - h_off;
+                for (; k < cnt && h_off[k] < hi; ++k) {
+                    const uint64_t o = order[pos + k];
+                    if (h_len[k]) memcpy(b.h_stage + h_off[k], hbase + off[o], h_len[k]);
+                }
+            });
+            if (bytes) CU(cudaMemcpyAsync(b.d_data, b.h_stage, bytes, cudaMemcpyHostToDevice, ctx->s_copy));
+        }
+        CU(cudaMemcpyAsync(b.d_meta, b.h_meta, cnt * 16, cudaMemcpyHostToDevice, ctx->s_copy));
+        CU(cudaEventRecord(ctx->ev_h2d[w % NBUF], ctx->s_copy));
+        CU(cudaStreamWaitEvent(ctx->s_comp, ctx->ev_h2d[w % NBUF], 0));
+        cas::BatchArgs a{};
+        a.base = b.d_data;
+        a.off = b.d_meta;
+        a.len = b.d_meta + cnt;
+        a.n = cnt;
+        a.out = b.d_dig;
+        if ((rc = launch_batch(ctx, a, ctx->s_comp))) return rc;
+        CU(cudaMemcpyAsync(b.h_dig, b.d_dig, cnt * 32, cudaMemcpyDeviceToHost, ctx->s_comp));
+        CU(cudaEventRecord(b.ev_done, ctx->s_comp));
+        b.busy = true;
+        pos += cnt;
+        ++w;
+    }
+    for (int i = 0; i < NBUF; ++i)
+        if ((rc = drain(ctx->buf[(w + i) % NBUF]))) return rc;
+    return CAS_OK;
+}
+
+}  // extern "C"

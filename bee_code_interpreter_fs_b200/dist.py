@@ -1,0 +1,89 @@
+"""torch.distributed plumbing for multi-GPU runs: rendezvous, barrier, max-over-ranks,
+and gathering per-rank digests.  The data path has no collective (objects are
+independent); these helpers only synchronise timing and collect 32-byte results.
+Works with backend "nccl" (one rank per GPU) and "gloo" (CPU tests)."""
+from __future__ import annotations
+
+import os
+
+import numpy as np
+
+
+def env_world() -> tuple[int, int, int]:
+    """(rank, local_rank, world_size) from the torchrun environment, (0, 0, 1) without it."""
+    return (int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)))
+
+
+def init(backend: str | None = None) -> tuple[int, int, int]:
+    import torch
+    import torch.distributed as dist
+
+    rank, local_rank, world = env_world()
+    if world > 1 and not dist.is_initialized():
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29531")
+        backend = backend or ("nccl" if torch.cuda.is_available() else "gloo")
+        if backend == "nccl":
+            torch.cuda.set_device(local_rank)
+            dist.init_process_group(backend, device_id=torch.device("cuda", local_rank))
+        else:
+            dist.init_process_group(backend)
+    return rank, local_rank, world
+
+
+def _device():
+    import torch
+    import torch.distributed as dist
+
+    if dist.is_initialized() and dist.get_backend() == "nccl":
+        return torch.device("cuda", torch.cuda.current_device())
+    return torch.device("cpu")
+
+
+def barrier() -> None:
+    import torch.distributed as dist
+
+    if dist.is_initialized():
+        dist.barrier()
+
+
+def max_over_ranks(value: float) -> float:
+    import torch
+    import torch.distributed as dist
+
+    if not dist.is_initialized():
+        return float(value)
+    t = torch.tensor([float(value)], dtype=torch.float64, device=_device())
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def sum_over_ranks(value: float) -> float:
+    import torch
+    import torch.distributed as dist
+
+    if not dist.is_initialized():
+        return float(value)
+    t = torch.tensor([float(value)], dtype=torch.float64, device=_device())
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    return float(t.item())
+
+
+def gather_digests(local: np.ndarray, counts: list[int]) -> np.ndarray:
+    """Concatenate per-rank (k_r, 32) digest arrays in rank order on every rank."""
+    import torch
+    import torch.distributed as dist
+
+    local = np.ascontiguousarray(local, dtype=np.uint8).reshape(-1, 32)
+    if not dist.is_initialized():
+        return local
+    world = dist.get_world_size()
+    if len(counts) != world or counts[dist.get_rank()] != local.shape[0]:
+        raise ValueError("counts do not describe the shards")
+    dev = _device()
+    width = max(counts) if counts else 0
+    pad = torch.zeros((max(width, 1), 32), dtype=torch.uint8, device=dev)
+    pad[: local.shape[0]] = torch.from_numpy(local).to(dev)
+    parts = [torch.empty_like(pad) for _ in range(world)]
+    dist.all_gather(parts, pad)
+    return np.concatenate([p[:c].cpu().numpy() for p, c in zip(parts, counts)], axis=0)

@@ -1,0 +1,242 @@
+"""GPU SHA-256 hashers over the C ABI (include/b200cas.h).
+
+``GpuHasher`` is one device; ``MultiGpuHasher`` shards a batch by object over
+several devices from one process (one host thread per device, no collective).
+PyTorch is used only for device buffers and stream handles.
+"""
+from __future__ import annotations
+
+import ctypes
+import threading
+from typing import Sequence
+
+import numpy as np
+
+from . import _ffi, shard
+from ._ffi import CasError
+
+BytesLike = bytes | bytearray | memoryview | np.ndarray
+
+
+def _addresses(objs: Sequence[BytesLike]) -> tuple[np.ndarray, np.ndarray, list]:
+    """Host addresses and lengths of the objects, without copying them."""
+    n = len(objs)
+    length = np.fromiter((len(o) if not isinstance(o, np.ndarray) else o.nbytes for o in objs), dtype=np.uint64, count=n)
+    keep: list = []
+    if all(type(o) is bytes for o in objs):
+        arr = (ctypes.c_char_p * n)(*objs)  # pointers into the bytes objects themselves
+        addr = np.frombuffer(arr, dtype=np.uint64, count=n).copy() if n else np.zeros(0, np.uint64)
+        keep.append(arr)
+    else:
+        addr = np.zeros(n, dtype=np.uint64)
+        for i, o in enumerate(objs):
+            if isinstance(o, np.ndarray):
+                a = np.ascontiguousarray(o).view(np.uint8).reshape(-1)
+            else:
+                a = np.frombuffer(o, dtype=np.uint8)
+            keep.append(a)
+            addr[i] = a.ctypes.data if a.size else 0
+    return addr, length, keep
+
+
+class GpuHasher:
+    """SHA-256 of batches of objects on one B200."""
+
+    def __init__(self, device: int = 0):
+        self._lib = _ffi.load()
+        self._ctx = ctypes.c_void_p()
+        rc = self._lib.cas_create(int(device), ctypes.byref(self._ctx))
+        if rc != _ffi.CAS_OK:
+            msg = (self._lib.cas_last_error(None) or b"").decode()
+            self._ctx = ctypes.c_void_p()
+            raise CasError(rc, msg)
+        self.device = int(device)
+        self._lock = threading.Lock()
+
+    # -- plumbing ---------------------------------------------------------
+    def _check(self, rc: int) -> None:
+        if rc != _ffi.CAS_OK:
+            raise CasError(rc, (self._lib.cas_last_error(self._ctx) or b"").decode())
+
+    def close(self) -> None:
+        if getattr(self, "_ctx", None) and self._ctx.value:
+            self._lib.cas_destroy(self._ctx)
+            self._ctx = ctypes.c_void_p()
+
+    def __del__(self):  # pragma: no cover - best effort
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def set_option(self, key: int, value: int) -> None:
+        self._check(self._lib.cas_set_option(self._ctx, key, int(value)))
+
+    def get_option(self, key: int) -> int:
+        v = ctypes.c_int64()
+        self._check(self._lib.cas_get_option(self._ctx, key, ctypes.byref(v)))
+        return v.value
+
+    def device_info(self) -> dict:
+        sm, khz, mem = ctypes.c_int(), ctypes.c_int(), ctypes.c_uint64()
+        self._check(self._lib.cas_device_info(self._ctx, ctypes.byref(sm), ctypes.byref(khz), ctypes.byref(mem)))
+        return {"sm_count": sm.value, "sm_clock_khz": khz.value, "mem_bytes": mem.value}
+
+    @property
+    def launch_count(self) -> int:
+        return int(self._lib.cas_launch_count(self._ctx))
+
+    @staticmethod
+    def _stream_handle(stream) -> int:
+        if stream is None:
+            return 0
+        return int(getattr(stream, "cuda_stream", stream))
+
+    # -- host buffers (end-to-end path) -------------------------------------
+    def digest_packed(self, base, off, length) -> np.ndarray:
+        """Digests of ``base[off[i]:off[i]+length[i]]``; ``base`` is host memory
+        (numpy array, pinned torch tensor, or None for absolute addresses)."""
+        off = np.ascontiguousarray(off, dtype=np.uint64)
+        length = np.ascontiguousarray(length, dtype=np.uint64)
+        n = int(off.shape[0])
+        if length.shape[0] != n:
+            raise ValueError("off and length differ in size")
+        out = np.empty((n, 32), dtype=np.uint8)
+        if base is None:
+            bptr = 0
+        elif isinstance(base, np.ndarray):
+            bptr = base.ctypes.data
+        elif hasattr(base, "data_ptr"):
+            if base.is_cuda:
+                raise ValueError("digest_packed takes host memory; use digest_device for device tensors")
+            bptr = base.data_ptr()
+        else:
+            bptr = int(base)
+        with self._lock:
+            self._check(self._lib.cas_hash_host(self._ctx, bptr, off.ctypes.data, length.ctypes.data, n, out.ctypes.data))
+        return out
+
+    def digest_many(self, objs: Sequence[BytesLike]) -> np.ndarray:
+        """(n, 32) uint8 digests of a list of bytes-like objects (no Python-side copy)."""
+        if len(objs) == 0:
+            return np.empty((0, 32), dtype=np.uint8)
+        addr, length, keep = _addresses(objs)
+        out = self.digest_packed(None, addr, length)
+        del keep
+        return out
+
+    def hash_many(self, objs: Sequence[BytesLike]) -> list[str]:
+        """Object ids (64 lowercase hex characters) of a batch of objects."""
+        return [row.tobytes().hex() for row in self.digest_many(objs)]
+
+    def hash_one(self, data: BytesLike) -> str:
+        return self.hash_many([data])[0]
+
+    # -- device buffers (kernel-only path) ------------------------------------
+    def digest_device(self, base, off, length, order=None, out=None, stream=None):
+        """Hash objects resident in device memory. ``base`` is a CUDA uint8 tensor (or
+        pointer), ``off``/``length`` CUDA int64/uint64 tensors; returns a CUDA (n, 32)
+        uint8 tensor. Asynchronous on ``stream`` (a torch stream) or the current stream."""
+        import torch
+
+        n = int(off.numel())
+        dev = off.device
+        if out is None:
+            out = torch.empty((n, 32), dtype=torch.uint8, device=dev)
+        if stream is None:
+            stream = torch.cuda.current_stream(dev)
+        bptr = base.data_ptr() if hasattr(base, "data_ptr") else int(base)
+        optr = order.data_ptr() if order is not None else 0
+        with self._lock:
+            self._check(self._lib.cas_hash_device(self._ctx, bptr, off.data_ptr(), length.data_ptr(), optr, n,
+                                                  out.data_ptr(), self._stream_handle(stream)))
+        return out
+
+    def digest_device_uniform(self, base, stride: int, length: int, n: int, out=None, stream=None):
+        """Uniform layout: object i at ``base + i*stride``, ``length`` bytes each."""
+        import torch
+
+        dev = base.device if hasattr(base, "device") else torch.device("cuda", self.device)
+        if out is None:
+            out = torch.empty((n, 32), dtype=torch.uint8, device=dev)
+        if stream is None:
+            stream = torch.cuda.current_stream(dev)
+        bptr = base.data_ptr() if hasattr(base, "data_ptr") else int(base)
+        with self._lock:
+            self._check(self._lib.cas_hash_device_uniform(self._ctx, bptr, int(stride), int(length), int(n),
+                                                          out.data_ptr(), self._stream_handle(stream)))
+        return out
+
+    def gen_synthetic(self, dst, seed: int, first_obj: int, n: int, length: int, stride: int | None = None, stream=None):
+        """Fill ``dst`` (CUDA uint8 tensor) with synthetic objects first_obj..first_obj+n."""
+        import torch
+
+        stride = length if stride is None else stride
+        need = (n - 1) * stride + length if n else 0
+        if dst.numel() * dst.element_size() < need:
+            raise ValueError("destination tensor too small")
+        if stream is None:
+            stream = torch.cuda.current_stream(dst.device)
+        with self._lock:
+            self._check(self._lib.cas_gen_synthetic(self._ctx, dst.data_ptr(), int(seed), int(first_obj), int(n),
+                                                    int(length), int(stride), self._stream_handle(stream)))
+        return dst
+
+    def int32_peak(self, mode: int = 0, steps: int = 4096) -> tuple[float, float]:
+        """(thread-level integer instructions per second, kernel ms) of the pipe probe."""
+        ops, ms = ctypes.c_double(), ctypes.c_double()
+        with self._lock:
+            self._check(self._lib.cas_int32_peak(self._ctx, int(mode), int(steps), ctypes.byref(ops), ctypes.byref(ms)))
+        return ops.value, ms.value
+
+
+class MultiGpuHasher:
+    """Shards a batch by object across several devices of one node (no collective)."""
+
+    def __init__(self, devices: Sequence[int] | None = None):
+        if devices is None:
+            import torch
+
+            devices = list(range(torch.cuda.device_count()))
+        if not devices:
+            raise CasError(_ffi.CAS_E_NODEVICE, "no CUDA device is visible (this engine has no CPU fallback)")
+        self.hashers = [GpuHasher(d) for d in devices]
+
+    def close(self) -> None:
+        for h in self.hashers:
+            h.close()
+
+    def digest_many(self, objs: Sequence[BytesLike]) -> np.ndarray:
+        n = len(objs)
+        if n == 0:
+            return np.empty((0, 32), dtype=np.uint8)
+        addr, length, keep = _addresses(objs)
+        parts = shard.assign(length, len(self.hashers))
+        results: list = [None] * len(self.hashers)
+        errors: list = []
+
+        def run(r: int) -> None:
+            try:
+                idx = parts[r]
+                results[r] = self.hashers[r].digest_packed(None, addr[idx], length[idx])
+            except Exception as e:  # noqa: BLE001 - re-raised below
+                errors.append(e)
+
+        threads = [threading.Thread(target=run, args=(r,)) for r in range(len(self.hashers))]
+        for t in threads:
+            t.start()
+        for t in threads:
+            t.join()
+        del keep
+        if errors:
+            raise errors[0]
+        return shard.scatter_back(parts, results, n)
+
+    def hash_many(self, objs: Sequence[BytesLike]) -> list[str]:
+        return [row.tobytes().hex() for row in self.digest_many(objs)]

@@ -1,0 +1,240 @@
+"""Content-addressed object store: a drop-in for the reference's ``Storage``.
+
+Mirrors ``/root/reference/src/code_interpreter/services/storage.py:34-101`` --
+same constructor, same six methods, same error behaviour -- with one change the
+reference's own docstring (storage.py:36) asks for: the id of an object is the
+SHA-256 of its bytes (64 lowercase hex characters, the shape
+``secrets.token_hex(32)`` has at storage.py:52), computed on the GPU in batches.
+
+Consequences of content-derived ids:
+* the id is known only when the last byte has arrived, so ``writer()`` spools
+  to a temporary file and renames it to ``<dir>/<sha256hex>`` on close;
+  ``.hash`` is set at close, which is when the reference's caller reads it
+  (services/kubernetes_code_executor.py:146);
+* equal content gives equal ids: a second write of the same bytes is a no-op.
+
+Concurrent finalisations (the ``asyncio.gather`` over changed files at
+kubernetes_code_executor.py:149-154) are coalesced into one GPU batch by
+``_Batcher``; the blocking CUDA call runs in a worker thread, off the event loop.
+Additive API: ``hash_many`` and ``write_many`` take whole batches.
+"""
+from __future__ import annotations
+
+import asyncio
+import os
+import secrets
+from contextlib import asynccontextmanager
+from typing import AsyncIterator, Protocol, Sequence
+
+from anyio import Path
+from pydantic import validate_call
+
+from .hasher import GpuHasher
+from .validation import Hash
+
+
+class ObjectReader(Protocol):
+    async def read(self, size: int = -1) -> bytes: ...
+
+
+class ObjectWriter(Protocol):
+    hash: str
+
+    async def write(self, data: bytes) -> None: ...
+
+
+class _Batcher:
+    """Collects ``hash(data)`` requests that arrive within ``window`` seconds of
+    each other (or until ``max_batch`` are waiting) and hashes them in one call."""
+
+    def __init__(self, hasher, window: float, max_batch: int):
+        self._hasher = hasher
+        self._window = window
+        self._max_batch = max_batch
+        self._pending: list[tuple[bytes, asyncio.Future]] = []
+        self._timer: asyncio.TimerHandle | None = None
+        self._lock: asyncio.Lock | None = None
+        self.batches = 0  # number of GPU batches issued (observable in tests)
+
+    async def hash(self, data: bytes) -> str:
+        loop = asyncio.get_running_loop()
+        fut: asyncio.Future = loop.create_future()
+        self._pending.append((data, fut))
+        if len(self._pending) >= self._max_batch:
+            self._fire(loop)
+        elif self._timer is None:
+            self._timer = loop.call_later(self._window, self._fire, loop)
+        return await fut
+
+    def _fire(self, loop: asyncio.AbstractEventLoop) -> None:
+        if self._timer is not None:
+            self._timer.cancel()
+            self._timer = None
+        batch, self._pending = self._pending, []
+        if batch:
+            loop.create_task(self._run(batch))
+
+    async def _run(self, batch: list[tuple[bytes, asyncio.Future]]) -> None:
+        if self._lock is None:
+            self._lock = asyncio.Lock()
+        try:
+            async with self._lock:  # one batch on the device context at a time
+                self.batches += 1
+                ids = await asyncio.get_running_loop().run_in_executor(
+                    None, self._hasher.hash_many, [d for d, _ in batch]
+                )
+            for (_, fut), object_id in zip(batch, ids):
+                if not fut.done():
+                    fut.set_result(object_id)
+        except BaseException as e:  # noqa: BLE001 - an engine failure must reach every waiter
+            for _, fut in batch:
+                if not fut.done():
+                    fut.set_exception(e if isinstance(e, Exception) else RuntimeError(str(e)))
+            if not isinstance(e, Exception):
+                raise
+
+
+class _SpoolWriter:
+    """What ``Storage.writer()`` yields: ``write`` appends a chunk, ``hash`` is set on close."""
+
+    def __init__(self, file):
+        self._file = file
+        self._chunks: list[bytes] = []
+        self.hash: str = ""
+
+    async def write(self, data: bytes) -> None:
+        data = bytes(data)
+        self._chunks.append(data)
+        await self._file.write(data)
+
+    def _content(self) -> bytes:
+        return self._chunks[0] if len(self._chunks) == 1 else b"".join(self._chunks)
+
+
+class Storage:
+    """
+    Storage is a collection of objects. Objects consist of binary data and are identified by their SHA-256 hash.
+
+    Backed by the filesystem: each object is a file named by its id under ``storage_path``.
+    """
+
+    def __init__(self, storage_path: str, hasher=None, device: int = 0, batch_window: float = 0.002,
+                 max_batch: int = 4096):
+        self.storage_path = Path(storage_path)
+        # No fallback: if the CUDA library or a B200 is missing this raises.
+        self._hasher = hasher if hasher is not None else GpuHasher(device)
+        self._batcher = _Batcher(self._hasher, batch_window, max_batch)
+
+    @property
+    def hasher(self):
+        return self._hasher
+
+    @property
+    def gpu_batches(self) -> int:
+        return self._batcher.batches
+
+    async def _publish(self, tmp: Path, object_id: str) -> None:
+        target = self.storage_path / object_id
+        if await target.exists():
+            await tmp.unlink(missing_ok=True)  # same content already stored
+        else:
+            await tmp.rename(target)  # atomic within the store directory
+
+    @asynccontextmanager
+    async def writer(self) -> AsyncIterator[ObjectWriter]:
+        """
+        Async context manager for writing a new object to the storage.
+
+        The final hash can be retrieved by using the `.hash` attribute once the
+        context has been left (the id depends on every byte written).
+        """
+        await self.storage_path.mkdir(parents=True, exist_ok=True)
+        tmp = self.storage_path / f".tmp-{secrets.token_hex(16)}"
+        file = await tmp.open("wb")
+        spool = _SpoolWriter(file)
+        try:
+            try:
+                yield spool
+            finally:
+                await file.aclose()
+            spool.hash = await self._batcher.hash(spool._content())
+            await self._publish(tmp, spool.hash)
+        except BaseException:
+            await tmp.unlink(missing_ok=True)
+            raise
+
+    async def write(self, data: bytes) -> str:
+        """
+        Writes the data to the storage and returns the hash of the object.
+        """
+        async with self.writer() as f:
+            await f.write(data)
+        return f.hash
+
+    async def hash_many(self, objects: Sequence[bytes]) -> list[str]:
+        """Ids of a batch of objects, one GPU batch, nothing stored."""
+        if not objects:
+            return []
+        return await asyncio.get_running_loop().run_in_executor(None, self._hasher.hash_many, list(objects))
+
+    async def write_many(self, objects: Sequence[bytes]) -> list[str]:
+        """Stores a batch of objects and returns their ids (one GPU batch)."""
+        ids = await self.hash_many(objects)
+        await self.storage_path.mkdir(parents=True, exist_ok=True)
+        for data, object_id in zip(objects, ids):
+            if await (self.storage_path / object_id).exists():
+                continue
+            tmp = self.storage_path / f".tmp-{secrets.token_hex(16)}"
+            try:
+                await tmp.write_bytes(data)
+                await self._publish(tmp, object_id)
+            except BaseException:
+                await tmp.unlink(missing_ok=True)
+                raise
+        return ids
+
+    @asynccontextmanager
+    @validate_call
+    async def reader(self, object_hash: Hash) -> AsyncIterator[ObjectReader]:
+        """
+        Async context manager that opens an object for reading.
+        """
+        target_file = self.storage_path / object_hash
+        if not object_hash or not await target_file.exists():
+            raise FileNotFoundError(f"File not found: {object_hash}")
+        async with await target_file.open("rb") as f:
+            yield f
+
+    @validate_call
+    async def read(self, object_hash: Hash) -> bytes:
+        """
+        Reads the object with the given hash and returns it.
+        """
+        async with self.reader(object_hash) as f:
+            return await f.read()
+
+    @validate_call
+    async def exists(self, object_hash: Hash) -> bool:
+        """
+        Check if an object with the given hash exists in the storage.
+        """
+        return await (self.storage_path / object_hash).exists()
+
+    @validate_call
+    async def delete(self, object_hash: Hash) -> None:
+        """
+        Delete an object with the given hash from the storage.
+        """
+        file_path = self.storage_path / object_hash
+        if await file_path.exists():
+            await file_path.unlink()
+        else:
+            raise FileNotFoundError(f"File not found: {object_hash}")
+
+    async def verify(self, object_hashes: Sequence[str]) -> dict[str, bool]:
+        """Re-hashes stored objects in one GPU batch: id -> (content still matches id)."""
+        present = [h for h in object_hashes if await self.exists(h)]
+        blobs = [await (self.storage_path / h).read_bytes() for h in present]
+        ids = await self.hash_many(blobs)
+        ok = {h: (h == got) for h, got in zip(present, ids)}
+        return {h: ok.get(h, False) for h in object_hashes}

@@ -1,0 +1,110 @@
+/*
+ * b200cas.h -- C ABI of the B200 batched SHA-256 content-addressing engine.
+ *
+ * Drop-in boundary.  The reference (bee-code-interpreter-fs) has no FFI: its
+ * object store is the Python class `Storage`
+ * (/root/reference/src/code_interpreter/services/storage.py:34-101), built once
+ * in ApplicationContext.file_storage (application_context.py:67-70).  The id of
+ * an object is fixed in `Storage.writer` (storage.py:44-55, storage.py:52) and
+ * returned by `Storage.write` (storage.py:57-63); the Execute call maps
+ * path -> id for every changed file (services/kubernetes_code_executor.py:138-154).
+ * This library is what a binding for that id-assignment step links against:
+ * plain pointers and sizes, no torch or Python types.  Our own host code binds
+ * it with ctypes (bee_code_interpreter_fs_b200/_ffi.py); INTEGRATION.md shows
+ * the stub a maintainer of the reference would add.
+ *
+ * Conventions: every function returns 0 on success or a negative CAS_E_* code;
+ * the message is available from cas_last_error().  A context belongs to one
+ * device and must not be used from two host threads at once.  Digests are the
+ * 32 raw bytes of SHA-256 (FIPS 180-4), bit-exact with hashlib.sha256; hex
+ * encoding (the 64-character id of storage.py:52's shape) is done by the caller.
+ * There is no CPU fallback: without a usable CUDA device every call fails.
+ */
+#ifndef B200CAS_H
+#define B200CAS_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CAS_OK 0
+#define CAS_E_CUDA (-1)     /* a CUDA runtime call failed */
+#define CAS_E_ARG (-2)      /* invalid argument */
+#define CAS_E_NOMEM (-3)    /* host or device allocation failed */
+#define CAS_E_NODEVICE (-4) /* no CUDA device / wrong architecture */
+
+typedef struct cas_ctx cas_ctx;
+
+/* Option keys for cas_set_option / cas_get_option. */
+#define CAS_OPT_KERNEL 1       /* load path: 0 = per-lane read-only loads, 1 = per-lane TMA bulk copies,
+                                  2 = TMA 2-D tiles for uniform layouts (per-lane loads otherwise) */
+#define CAS_OPT_FMA_LEVEL 2    /* 0..3: how many of the adds run on the FMA pipe (sha256_sm100.cuh) */
+#define CAS_OPT_WAVE_BYTES 3   /* host path: bytes staged per wave (rounded to 1 MiB) */
+#define CAS_OPT_PACK_THREADS 4 /* host path: threads that pack objects into pinned staging */
+#define CAS_OPT_CTAS_PER_SM 5  /* resident 256-thread CTAs per SM the kernels are compiled for: 4, 3 or 2
+                                  (register budget 64, 80 or 128 per thread) */
+
+/* Create / destroy the per-device context (streams, staging buffers are made
+ * lazily).  Replaces nothing in the reference; it is the state a
+ * `Storage(storage_path)` instance would own (storage.py:41-42). */
+int cas_create(int device, cas_ctx** out);
+void cas_destroy(cas_ctx* ctx);
+/* Last error text of `ctx`, or of the last failed cas_create when ctx is NULL. */
+const char* cas_last_error(const cas_ctx* ctx);
+int cas_set_option(cas_ctx* ctx, int key, int64_t value);
+int cas_get_option(const cas_ctx* ctx, int key, int64_t* value);
+/* sm_count, max SM clock (kHz), total device memory (bytes). Any pointer may be NULL. */
+int cas_device_info(const cas_ctx* ctx, int* sm_count, int* sm_clock_khz, uint64_t* mem_bytes);
+
+/*
+ * Id assignment for a batch of objects held in HOST memory: the arithmetic the
+ * reference's docstring assigns to Storage.writer/Storage.write
+ * (storage.py:36, :44-63), for the n objects base[off[i] .. off[i]+len[i]).
+ * `base` may be NULL, in which case off[i] are absolute host addresses (how a
+ * list of Python `bytes` is passed without copying).  Synchronous: host->device
+ * copies (pinned, double-buffered, overlapped with the kernel), the kernel and
+ * the device->host copy of the digests all happen inside the call.  Objects are
+ * borrowed for the call only.  out32n receives n*32 bytes, object-major.
+ */
+int cas_hash_host(cas_ctx* ctx, const void* base, const uint64_t* off, const uint64_t* len, uint64_t n,
+                  void* out32n);
+
+/*
+ * Same arithmetic for objects already resident in DEVICE memory (kernel only,
+ * asynchronous on `stream`, a cudaStream_t or NULL for the default stream).
+ * d_off/d_len are device arrays; d_order is NULL or a device permutation: lane t
+ * hashes object d_order[t] (a longest-first order keeps lanes of a warp the same
+ * length).  d_out receives n*32 bytes.  Objects starting on a 16-byte boundary
+ * take the fast path; any alignment is correct.
+ */
+int cas_hash_device(cas_ctx* ctx, const void* d_base, const uint64_t* d_off, const uint64_t* d_len,
+                    const uint32_t* d_order, uint64_t n, void* d_out, void* stream);
+
+/* Uniform layout: object i is d_base[i*stride .. i*stride+len). The shape of
+ * BASELINE.json configs 2 and 3 (1M x 4 KiB / 64 KiB). */
+int cas_hash_device_uniform(cas_ctx* ctx, const void* d_base, uint64_t stride, uint64_t len, uint64_t n,
+                            void* d_out, void* stream);
+
+/* Synthetic benchmark objects generated on the device:
+ * object first_obj+i at d_dst[i*stride .. i*stride+len), byte-identical to
+ * oracle/sha256_oracle.py:synth_object(seed, first_obj+i, len). */
+int cas_gen_synthetic(cas_ctx* ctx, void* d_dst, uint64_t seed, uint64_t first_obj, uint64_t n, uint64_t len,
+                      uint64_t stride, void* stream);
+
+/* Integer-pipe throughput probe (roofline denominator). mode: see csrc/peak.cuh.
+ * Returns thread-level instructions per second and the kernel time. */
+int cas_int32_peak(cas_ctx* ctx, int mode, int steps, double* lane_ops_per_s, double* ms);
+
+/* Number of kernels this context has launched since creation. */
+uint64_t cas_launch_count(const cas_ctx* ctx);
+
+/* Library build tag, e.g. "b200cas 0.1 sm_100a". */
+const char* cas_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200CAS_H */

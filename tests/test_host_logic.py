@@ -1,0 +1,188 @@
+"""Host-side logic that needs no GPU: sharding, id/path types, the Storage drop-in's
+file semantics (with the oracle standing in for the device, as tests may)."""
+import asyncio
+import hashlib
+import os
+import re
+
+import numpy as np
+import pytest
+from pydantic import TypeAdapter, ValidationError
+
+from bee_code_interpreter_fs_b200 import shard
+from bee_code_interpreter_fs_b200.storage import Storage
+from bee_code_interpreter_fs_b200.validation import AbsolutePath, Hash
+
+
+def run(coro):
+    return asyncio.run(coro)
+
+
+# ----------------------------------------------------------------- id types --
+def test_hash_and_path_types_match_reference(storage_behaviour):
+    ha, pa = TypeAdapter(Hash), TypeAdapter(AbsolutePath)
+
+    def ok(adapter, v):
+        try:
+            adapter.validate_python(v)
+            return True
+        except ValidationError:
+            return False
+
+    for v, want in storage_behaviour["hash_accepts"].items():
+        assert ok(ha, v) == want, v
+    for v, want in storage_behaviour["path_accepts"].items():
+        assert ok(pa, v) == want, v
+
+
+# ------------------------------------------------------------------ sharding --
+def test_nblocks():
+    assert shard.nblocks([0, 55, 56, 64, 4096, 65536, 1 << 30]).tolist() == [1, 1, 2, 2, 65, 1025, 16777217]
+
+
+def test_contiguous_ranges_cover():
+    for n in (0, 1, 7, 1 << 20):
+        for w in (1, 2, 4, 8):
+            r = shard.contiguous_ranges(n, w)
+            assert r[0][0] == 0 and r[-1][1] == n
+            assert all(a[1] == b[0] for a, b in zip(r, r[1:]))
+            assert max(hi - lo for lo, hi in r) - min(hi - lo for lo, hi in r) <= 1
+
+
+def test_lpt_balances_by_compressions():
+    rng = np.random.default_rng(0xB200)
+    lengths = np.floor(2 ** rng.uniform(10, 26, size=4096)).astype(np.uint64)
+    for w in (2, 4, 8):
+        parts = shard.assign(lengths, w)
+        assert sorted(np.concatenate(parts).tolist()) == list(range(4096))
+        loads = [int(shard.nblocks(lengths[p]).sum()) for p in parts]
+        assert max(loads) <= 1.02 * (sum(loads) / w) + int(shard.nblocks(lengths.max()))
+
+
+def test_scatter_back_roundtrip():
+    lengths = np.array([5, 100000, 3, 70000, 64, 1], dtype=np.uint64)
+    parts = shard.assign(lengths, 3)
+    digs = [np.tile((p % 251).astype(np.uint8)[:, None], (1, 32)) for p in parts]
+    out = shard.scatter_back(parts, digs, 6)
+    assert out[:, 0].tolist() == [0, 1, 2, 3, 4, 5]
+    with pytest.raises(ValueError):
+        shard.scatter_back(parts[:-1], digs[:-1], 6)
+
+
+# ------------------------------------------------------------------- Storage --
+def test_storage_matches_reference_behaviour(tmp_path, oracle_hasher, storage_behaviour):
+    ref = storage_behaviour["storage"]
+
+    async def go():
+        st = Storage(str(tmp_path / "nested" / "store"), hasher=oracle_hasher)
+        rec = {}
+        i1 = await st.write(b"abc")
+        i2 = await st.write(b"abc")
+        rec["write_returns_str"] = isinstance(i1, str)
+        rec["id_matches_regex"] = bool(re.fullmatch(ref["id_regex"], i1))
+        rec["file_named_by_id"] = os.path.isfile(tmp_path / "nested" / "store" / i1)
+        rec["read_roundtrip"] = (await st.read(i1)) == b"abc"
+        rec["exists_true"] = await st.exists(i1)
+        rec["exists_missing"] = await st.exists("0" * 64)
+        async with st.writer() as w:
+            await w.write(b"he")
+            await w.write(b"llo")
+        rec["writer_hash_after_close_is_str"] = isinstance(w.hash, str)
+        rec["writer_chunks_concatenate"] = (await st.read(w.hash)) == b"hello"
+        async with st.reader(i1) as r:
+            rec["reader_read_size"] = (await r.read(2)).decode()
+            rec["reader_read_rest"] = (await r.read()).decode()
+        for name, fn in (("read", st.read), ("delete", st.delete)):
+            try:
+                await fn("0" * 64)
+                rec[f"{name}_missing"] = None
+            except Exception as e:  # noqa: BLE001
+                rec[f"{name}_missing"] = {"type": type(e).__name__, "msg": str(e)}
+        try:
+            async with st.reader("0" * 64):
+                pass
+        except Exception as e:  # noqa: BLE001
+            rec["reader_missing"] = {"type": type(e).__name__, "msg": str(e)}
+        for name, fn in (("read", st.read), ("exists", st.exists), ("delete", st.delete)):
+            try:
+                await fn("a/b")
+                rec[f"{name}_bad_id"] = None
+            except Exception as e:  # noqa: BLE001
+                rec[f"{name}_bad_id"] = {"type": type(e).__name__}
+        await st.delete(i1)
+        rec["exists_after_delete"] = await st.exists(i1)
+        rec["empty_object_roundtrip"] = (await st.read(await st.write(b""))) == b""
+        # the deliberate difference: ids are the content's SHA-256, hence repeatable
+        assert i1 == i2 == hashlib.sha256(b"abc").hexdigest()
+        assert w.hash == hashlib.sha256(b"hello").hexdigest()
+        return rec
+
+    rec = run(go())
+    for key, got in rec.items():
+        assert got == ref[key], key
+    assert ref["reference_ids_are_random"] and not ref["reference_id_is_sha256"]
+
+
+def test_storage_leaves_no_temp_files_and_dedups(tmp_path, oracle_hasher):
+    async def go():
+        st = Storage(str(tmp_path), hasher=oracle_hasher)
+        ids = await asyncio.gather(*(st.write(b"same") for _ in range(5)))
+        assert len(set(ids)) == 1
+        with pytest.raises(RuntimeError):
+            async with st.writer() as w:
+                await w.write(b"partial")
+                raise RuntimeError("caller failed mid-stream")
+        return ids[0]
+
+    object_id = run(go())
+    assert sorted(os.listdir(tmp_path)) == [object_id]
+
+
+def test_concurrent_finalisations_coalesce_into_one_batch(tmp_path, oracle_hasher):
+    """The executor's download leg gathers over changed files
+    (kubernetes_code_executor.py:149-154): those writers must share a GPU batch."""
+
+    async def go():
+        st = Storage(str(tmp_path), hasher=oracle_hasher, batch_window=0.05)
+
+        async def download(i):
+            async with st.writer() as f:
+                for chunk in (b"chunk-%d-" % i, b"x" * i):
+                    await f.write(chunk)
+            return f.hash
+
+        ids = await asyncio.gather(*(download(i) for i in range(16)))
+        return st, ids
+
+    st, ids = run(go())
+    assert st.gpu_batches == 1 and oracle_hasher.calls == 1
+    for i, object_id in enumerate(ids):
+        assert object_id == hashlib.sha256(b"chunk-%d-" % i + b"x" * i).hexdigest()
+
+
+def test_write_many_and_verify(tmp_path, oracle_hasher):
+    async def go():
+        st = Storage(str(tmp_path), hasher=oracle_hasher)
+        objs = [os.urandom(n) for n in (0, 1, 100, 5000)]
+        ids = await st.write_many(objs)
+        assert ids == [hashlib.sha256(o).hexdigest() for o in objs]
+        assert [await st.read(i) for i in ids] == objs
+        (tmp_path / ids[2]).write_bytes(b"corrupted")
+        ok = await st.verify(ids + ["f" * 64])
+        assert ok == {ids[0]: True, ids[1]: True, ids[2]: False, ids[3]: True, "f" * 64: False}
+
+    run(go())
+
+
+def test_engine_failure_reaches_the_caller(tmp_path):
+    class Broken:
+        def hash_many(self, objs):
+            raise RuntimeError("device lost")
+
+    async def go():
+        st = Storage(str(tmp_path), hasher=Broken())
+        with pytest.raises(RuntimeError, match="device lost"):
+            await st.write(b"abc")
+
+    run(go())
+    assert os.listdir(tmp_path) == []
