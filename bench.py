@@ -1,0 +1,429 @@
+#!/usr/bin/env python
+"""Benchmark of the SHA-256 content-addressing path (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W]            # this engine
+    python bench.py --impl reference [--gpus N] [--steps K] ...    # hashlib on the host cores
+
+A step is one pass of the hot path over one batch of synthetic objects: by default
+BASELINE config 3's shape, 2^20 objects x 64 KiB = 64 GiB per GPU (the configuration
+the north-star target is quoted on; it fits one B200).  At N > 1 (torchrun, one rank per
+GPU) every rank hashes its own 2^20 objects -- weak scaling, no collective on the data
+path -- and `value` is all ranks' bytes over the slowest rank's time.
+
+value    kernel-only GB/s, inputs resident in HBM, CUDA events on the launch stream
+e2e      the same batch through cas_hash_host from pinned HOST memory (H2D + kernel + D2H
+         of the digests inside the timed region) -- the headline against the CPU arm
+roofline HBM view required by the bench contract, plus `int32_roofline`: the INT32-ALU
+         view that actually bounds this kernel, against a peak
+         measured in this run by csrc/peak.cuh
+One JSON line on stdout (rank 0); progress goes to stderr.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+SEED = 0xB200
+INSTR_PER_COMPRESSION = 1400  # SHF/LOP3/IADD3-shaped count per 64-byte block
+NOMINAL_SM_MHZ = 1965.0
+LANES_PER_SM_CLK = 64  # INT32 ALU pipe: 16 lanes x 4 sub-partitions
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+def nblocks(length: int) -> int:
+    return (length + 9 + 63) // 64
+
+
+def measured_peaks() -> dict:
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return json.load(f)
+    except OSError:
+        return {}
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks and throttle reasons of one GPU while a region runs."""
+
+    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index = index
+        self.rows: list[list[str]] = []
+        self.proc = None
+        self.thread = None
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            parts = [p.strip() for p in line.split(",")]
+            if len(parts) >= 7:
+                self.rows.append(parts)
+
+    def __exit__(self, *exc):
+        if self.proc:
+            time.sleep(0.15)
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except subprocess.TimeoutExpired:
+                self.proc.kill()
+            self.thread.join(timeout=2)
+
+    def summary(self) -> dict:
+        sm, mx, reasons = [], [], set()
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx.append(float(r[1]))
+            except ValueError:
+                continue
+            for name, val in zip(names, r[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def physical_gpu_index(local_rank: int) -> int:
+    vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+    if vis:
+        ids = [v for v in vis.split(",") if v.strip()]
+        if local_rank < len(ids) and ids[local_rank].strip().isdigit():
+            return int(ids[local_rank])
+    return local_rank
+
+
+def mem_available_bytes() -> int:
+    try:
+        with open("/proc/meminfo") as f:
+            for line in f:
+                if line.startswith("MemAvailable:"):
+                    return int(line.split()[1]) * 1024
+    except OSError:
+        pass
+    return 0
+
+
+def cgroup_limit_bytes() -> int:
+    for p in ("/sys/fs/cgroup/memory.max", "/sys/fs/cgroup/memory/memory.limit_in_bytes"):
+        try:
+            v = open(p).read().strip()
+            if v.isdigit():
+                return int(v)
+        except OSError:
+            pass
+    return 1 << 62
+
+
+# ------------------------------------------------------------------ CPU arm --
+def cpu_hashlib_rate(views, threads: int) -> float:
+    """GB/s of hashlib.sha256 over `views` with `threads` host threads."""
+    from oracle import sha256_oracle as oracle
+
+    total = sum(len(v) for v in views)
+    t0 = time.perf_counter()
+    oracle.hashlib_digests_mt(views, threads)
+    return total / (time.perf_counter() - t0) / 1e9
+
+
+def run_reference(args) -> None:
+    """The reference's CPU path for object ids as BASELINE.json names it: hashlib.sha256 on
+    the host cores, all of them, over a bounded sample of the same workload per step."""
+    import numpy as np
+
+    from oracle import sha256_oracle as oracle
+
+    rank = int(os.environ.get("RANK", 0))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    length = args.object_bytes
+    sample = max(cores * 8, min(args.objects, int(args.ref_sample_bytes // max(1, length))))
+    log(f"[reference] generating {sample} x {length} B on the host")
+    buf = oracle.synth_batch(SEED, 0, sample, length)
+    mv = memoryview(buf)
+    views = [mv[i * length:(i + 1) * length] for i in range(sample)]
+    want0 = oracle.hashlib_digests([views[0]])[0]
+    assert want0 == oracle.c_digests([bytes(views[0])])[0], "hashlib and the C port disagree"
+    for _ in range(args.warmup):
+        oracle.hashlib_digests_mt(views, cores)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        oracle.hashlib_digests_mt(views, cores)
+    dt = time.perf_counter() - t0
+    gbs = sample * length * args.steps / dt / 1e9
+    port = oracle.c_digests_packed(buf[: min(sample, 256) * length], np.arange(min(sample, 256), dtype=np.uint64) * length,
+                                   np.full(min(sample, 256), length, dtype=np.uint64))
+    assert port[0].tobytes() == want0
+    desc = f"{sample} of {args.objects} objects x {length} B per step, hashlib.sha256 on {cores} threads"
+    print(json.dumps({
+        "impl": "reference", "metric": "sha256_gb_per_s", "value": gbs, "unit": "GB/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
+        "config": workload_config(args, args.gpus),
+        "cpu_baseline": {"value": gbs, "unit": "GB/s", "cores": cores, "kind": "reference", "sample": desc},
+        "e2e": {"value": gbs, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }), flush=True)
+
+
+def workload_config(args, world: int) -> dict:
+    return {
+        "workload": f"BASELINE config 3 shape: {args.objects} synthetic objects x {args.object_bytes} B per GPU "
+                    f"(seed 0x{SEED:X}, counter-based generator), sharded by object, {world} GPU(s)",
+        "objects_per_gpu": args.objects, "object_bytes": args.object_bytes, "n_gpus": world,
+        "parallelism": f"object-sharded x{world}, no collective",
+        "l2": "inputs (64 GiB per GPU by default) are far larger than the 126 MB L2; no flush needed",
+    }
+
+
+# ------------------------------------------------------------------ GPU arm --
+def run_ours(args) -> None:
+    import numpy as np
+    import torch
+
+    from bee_code_interpreter_fs_b200 import GpuHasher, _ffi
+    from bee_code_interpreter_fs_b200 import dist as cdist
+    from oracle import sha256_oracle as oracle  # checker + cpu_baseline only
+
+    rank, local_rank, world = cdist.init()
+    if world != args.gpus:
+        log(f"[warn] --gpus {args.gpus} but WORLD_SIZE={world}; using {world}")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    h = GpuHasher(local_rank)
+    for key, val in ((_ffi.OPT_KERNEL, args.kernel), (_ffi.OPT_FMA_LEVEL, args.fma), (_ffi.OPT_CTAS_PER_SM, args.ctas)):
+        if val is not None:
+            h.set_option(key, val)
+    n, length = args.objects, args.object_bytes
+    first_obj = rank * n
+    total_bytes = n * length
+    stream = torch.cuda.Stream(dev)
+    log(f"[rank {rank}] generating {n} x {length} B = {total_bytes / 2**30:.1f} GiB on {torch.cuda.get_device_name(dev)}")
+    buf = torch.empty(total_bytes, dtype=torch.uint8, device=dev)
+    with torch.cuda.stream(stream):
+        h.gen_synthetic(buf, SEED, first_obj, n, length, stream=stream)
+    stream.synchronize()
+    out = torch.empty((n, 32), dtype=torch.uint8, device=dev)
+
+    # Measured integer-pipe peaks (roofline denominator), taken right before the timed region.
+    peak_alu, _ = h.int32_peak(0, 8192)
+    peak_mix, _ = h.int32_peak(4, 8192)
+
+    launches0 = h.launch_count
+    for _ in range(args.warmup):
+        h.digest_device_uniform(buf, length, length, n, out=out, stream=stream)
+    stream.synchronize()
+    cdist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(physical_gpu_index(local_rank)) as clk:
+        torch.cuda.synchronize()
+        launches_t0 = h.launch_count
+        with torch.cuda.stream(stream):
+            e0.record(stream)
+            for _ in range(args.steps):
+                h.digest_device_uniform(buf, length, length, n, out=out, stream=stream)
+            e1.record(stream)
+        stream.synchronize()
+        torch.cuda.synchronize()
+        timed_launches = h.launch_count - launches_t0
+    cdist.barrier()
+    my_ms = e0.elapsed_time(e1)
+    ms = cdist.max_over_ranks(my_ms)
+    clocks = clk.summary()
+    value = world * total_bytes * args.steps / (ms * 1e-3) / 1e9
+    log(f"[rank {rank}] kernel-only {total_bytes * args.steps / (my_ms * 1e-3) / 1e9:.1f} GB/s ({my_ms / args.steps:.2f} ms/step)")
+
+    # Bit-exactness gate: sampled objects and shard edges against hashlib on host-generated bytes.
+    dig = out.cpu().numpy()
+    rng = np.random.default_rng(rank)
+    sample_idx = sorted(set([0, 1, 31, 32, 255, 256, n - 1] + rng.integers(0, n, size=args.verify_objects).tolist()))
+    sample_idx = [i for i in sample_idx if 0 <= i < n]
+    for i in sample_idx:
+        want = oracle.hashlib_digests([oracle.synth_object(SEED, first_obj + i, length)])[0]
+        if dig[i].tobytes() != want:
+            log(f"[rank {rank}] DIGEST MISMATCH at object {i}: no throughput is reported")
+            sys.exit(1)
+    log(f"[rank {rank}] verified {len(sample_idx)} sampled digests against hashlib")
+
+    # ---- end to end: pinned host memory -> digests on the host --------------------------
+    avail = min(mem_available_bytes(), cgroup_limit_bytes())
+    local_world = int(os.environ.get("LOCAL_WORLD_SIZE", world))
+    budget = int(0.35 * avail / max(1, local_world))
+    host_objects = max(1, min(n, min(budget, args.e2e_host_bytes) // length))
+    passes = -(-n // host_objects)
+    host_objects = -(-n // passes)  # equal passes; the last may be shorter
+    log(f"[rank {rank}] e2e host buffer: {host_objects} objects ({host_objects * length / 2**30:.1f} GiB pinned), "
+        f"{passes} call(s) per step")
+    host = torch.empty(host_objects * length, dtype=torch.uint8, pin_memory=True)
+    host.copy_(buf[: host_objects * length])
+    torch.cuda.synchronize()
+    off = np.arange(host_objects, dtype=np.uint64) * length
+    lens = np.full(host_objects, length, dtype=np.uint64)
+
+    def e2e_step():
+        done, last = 0, None
+        while done < n:
+            m = min(host_objects, n - done)
+            last = h.digest_packed(host, off[:m], lens[:m])
+            done += m
+        return last
+
+    e2e_steps = max(1, min(args.steps, args.e2e_steps))
+    e2e_warm = max(1, min(args.warmup, 2))
+    for _ in range(e2e_warm):
+        e2e_dig = e2e_step()
+    k_chk = min(e2e_dig.shape[0], 4096)
+    if not (e2e_dig[:k_chk] == dig[:k_chk]).all():
+        log(f"[rank {rank}] E2E DIGEST MISMATCH: no throughput is reported")
+        sys.exit(1)
+    cdist.barrier()
+    torch.cuda.synchronize()
+    launches_e0 = h.launch_count
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    torch.cuda.synchronize()
+    e2e_s = cdist.max_over_ranks(time.perf_counter() - t0)
+    e2e_launches = h.launch_count - launches_e0
+    cdist.barrier()
+    e2e_value = world * total_bytes * e2e_steps / e2e_s / 1e9
+    log(f"[rank {rank}] end-to-end {total_bytes * e2e_steps / e2e_s / 1e9:.1f} GB/s")
+
+    # ---- CPU baseline beside it (rank 0, N = 1 only) -------------------------------------
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cores = os.cpu_count() or 1
+        mv = memoryview(host.numpy())
+        probe = [mv[i * length:(i + 1) * length] for i in range(min(host_objects, max(64, cores * 16)))]
+        rate = cpu_hashlib_rate(probe, cores)
+        k = int(max(len(probe), min(host_objects, rate * 1e9 * args.cpu_seconds / length)))
+        views = [mv[i * length:(i + 1) * length] for i in range(k)]
+        rate = cpu_hashlib_rate(views, cores)
+        one = cpu_hashlib_rate(views[: max(16, k // cores)], 1)
+        mport = min(k, 2048)
+        t0 = time.perf_counter()
+        port = oracle.c_digests_packed(host.numpy()[: mport * length], off[:mport], lens[:mport], threads=cores)
+        port_rate = mport * length / (time.perf_counter() - t0) / 1e9
+        assert (port == dig[:mport]).all(), "C port disagrees with the GPU digests"
+        cpu = {"value": rate, "unit": "GB/s", "cores": cores, "kind": "reference",
+               "sample": f"hashlib.sha256 (OpenSSL) over the first {k} of the {n} objects on {cores} threads, ~{args.cpu_seconds:.0f} s",
+               "single_thread_gb_s": one, "c_port_all_cores_gb_s": port_rate}
+        log(f"[cpu] hashlib {cores} threads {rate:.2f} GB/s, 1 thread {one:.2f} GB/s, C port {port_rate:.2f} GB/s")
+
+    if rank != 0:
+        return
+    per_launch_ms = ms / args.steps
+    compressions = n * nblocks(length)
+    int_rate = compressions * INSTR_PER_COMPRESSION / (per_launch_ms * 1e-3)
+    info = h.device_info()
+    nominal_peak = info["sm_count"] * LANES_PER_SM_CLK * NOMINAL_SM_MHZ * 1e6
+    peaks = measured_peaks()
+    hbm_peak = peaks.get("hbm_gbs", 6650.0)
+    alg_bytes = n * length + n * 32
+    hbm_achieved = alg_bytes / (per_launch_ms * 1e-3) / 1e9
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "dram_traffic.json")) as f:
+            t = json.load(f)
+            if t.get("objects") == n and t.get("object_bytes") == length:
+                traffic = t.get("dram_bytes_per_launch")
+    except (OSError, ValueError):
+        pass
+    line = {
+        "metric": "sha256_gb_per_s", "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": per_launch_ms, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u32", "data": "synthetic",
+        "config": workload_config(args, world),
+        "kernel": {"load_path": h.get_option(_ffi.OPT_KERNEL), "fma_level": h.get_option(_ffi.OPT_FMA_LEVEL),
+                   "ctas_per_sm": h.get_option(_ffi.OPT_CTAS_PER_SM)},
+        "roofline": {"bound": "hbm", "achieved": hbm_achieved, "peak": hbm_peak, "unit": "GB/s",
+                     "frac": hbm_achieved / hbm_peak, "traffic": traffic,
+                     "peak_source": "MEASURED_PEAKS.json (measured)" if "hbm_gbs" in peaks else "fallback",
+                     "note": "contract view; the kernel is INT32-ALU bound, see int32_roofline"},
+        "int32_roofline": {
+            "bound": "int32_alu", "instr_per_compression": INSTR_PER_COMPRESSION,
+            "compressions_per_launch": compressions, "achieved": int_rate / 1e12, "unit": "Tinstr/s",
+            "peak": peak_alu / 1e12, "frac": int_rate / peak_alu,
+            "peak_source": "cas_int32_peak mode 0 (SHF+LOP3+IADD3, ALU pipe only), this run",
+            "peak_nominal": nominal_peak / 1e12, "frac_of_nominal": int_rate / nominal_peak,
+            "peak_alu_plus_fma": peak_mix / 1e12,
+            "note": "adds run on the FMA pipe as IMAD, so the ALU-pipe roofline can be exceeded",
+        },
+        "clocks": {"sm_mhz": clocks["sm_mhz"], "sm_max_mhz": clocks["sm_max_mhz"], "reasons": clocks["reasons"],
+                   "samples": clocks["samples"]},
+        "e2e": {"value": e2e_value, "unit": "GB/s", "h2d_bytes_per_step": total_bytes,
+                "d2h_bytes_per_step": n * 32, "steps": e2e_steps, "host_buffer_bytes": host_objects * length,
+                "calls_per_step": passes, "timing": "host wall clock around synchronous cas_hash_host calls, max over ranks"},
+        "gpu_launches": int(timed_launches), "gpu_launches_e2e": int(e2e_launches),
+        "verified": f"{len(sample_idx)} sampled digests + e2e digests bit-exact vs hashlib",
+    }
+    if cpu:
+        line["cpu_baseline"] = cpu
+    print(json.dumps(line), flush=True)
+    h.close()
+
+
+def main() -> None:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", choices=("ours", "reference"), default="ours")
+    ap.add_argument("--objects", type=int, default=1 << 20)
+    ap.add_argument("--object-bytes", type=int, default=65536)
+    ap.add_argument("--kernel", type=int, default=None)
+    ap.add_argument("--fma", type=int, default=None)
+    ap.add_argument("--ctas", type=int, default=None)
+    ap.add_argument("--verify-objects", type=int, default=2048)
+    ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--e2e-host-bytes", type=int, default=64 << 30)
+    ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    ap.add_argument("--ref-sample-bytes", type=float, default=float(2 << 30))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "ours":
+        log("[warn] fewer than 3 warm-up steps breaks the timing rules")
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+    try:
+        import torch.distributed as dist
+
+        if dist.is_initialized():
+            dist.destroy_process_group()
+    except Exception:
+        pass
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,185 @@
+"""Parity of the CUDA path with the oracle, through the C ABI, on a B200.
+
+Bit-exact is the bar (integer/byte work): every digest is compared with hashlib.sha256
+(the oracle BASELINE.json names) on the same bytes.  Every load path (per-lane loads,
+per-lane TMA bulk copies, TMA 2-D tiles) and every FMA-pipe level is exercised.
+"""
+import hashlib
+
+import numpy as np
+import pytest
+import torch
+
+from bee_code_interpreter_fs_b200 import _ffi
+from oracle import sha256_oracle as oracle
+
+pytestmark = pytest.mark.gpu
+
+KERNELS = [0, 1, 2]
+FMA_LEVELS = [0, 1, 2, 3]
+
+
+def configure(h, kernel=None, fma=None, ctas=None):
+    if kernel is not None:
+        h.set_option(_ffi.OPT_KERNEL, kernel)
+    if fma is not None:
+        h.set_option(_ffi.OPT_FMA_LEVEL, fma)
+    if ctas is not None:
+        h.set_option(_ffi.OPT_CTAS_PER_SM, ctas)
+
+
+@pytest.fixture(autouse=True)
+def restore_defaults(hasher):
+    saved = {k: hasher.get_option(k) for k in (_ffi.OPT_KERNEL, _ffi.OPT_FMA_LEVEL, _ffi.OPT_CTAS_PER_SM,
+                                              _ffi.OPT_WAVE_BYTES)}
+    yield
+    for k, v in saved.items():
+        hasher.set_option(k, v)
+
+
+def hexes(digests):
+    return [bytes(d).hex() for d in np.asarray(digests)]
+
+
+# ------------------------------------------------------------ known answers --
+@pytest.mark.parametrize("kernel", KERNELS)
+@pytest.mark.parametrize("fma", FMA_LEVELS)
+def test_fips_and_boundary_vectors_host_path(hasher, kat, kernel, fma):
+    configure(hasher, kernel, fma)
+    msgs = [v["unit"].encode() * v["repeat"] for v in kat["fips"]] + [bytes(v["len"]) for v in kat["zeros"]]
+    want = [v["sha256"] for v in kat["fips"]] + [v["sha256"] for v in kat["zeros"]]
+    assert hasher.hash_many(msgs) == want
+
+
+@pytest.mark.parametrize("ctas", [2, 3, 4])
+def test_register_budget_variants(hasher, kat, ctas):
+    configure(hasher, ctas=ctas)
+    for kernel in KERNELS:
+        configure(hasher, kernel)
+        msgs = [bytes(v["len"]) for v in kat["zeros"]]
+        assert hasher.hash_many(msgs) == [v["sha256"] for v in kat["zeros"]]
+
+
+# ------------------------------------------------- device path, uniform layout --
+@pytest.mark.parametrize("kernel", KERNELS)
+@pytest.mark.parametrize("length,stride,n", [
+    (64, 64, 33), (4096, 4096, 1000), (65536, 65536, 70), (1000, 1008, 257), (55, 64, 64), (56, 64, 31),
+    (119, 128, 5), (4097, 4112, 300), (1, 16, 100), (0, 16, 3), (129, 129, 40), (8192, 16384, 513),
+])
+def test_uniform_device_path_matches_oracle(hasher, kernel, length, stride, n):
+    """Also proves the device generator emits the oracle's synthetic bytes."""
+    configure(hasher, kernel)
+    buf = torch.zeros(max(16, n * stride + 16), dtype=torch.uint8, device="cuda:0")
+    hasher.gen_synthetic(buf, 0xB200, 11, n, length, stride)
+    dig = hasher.digest_device_uniform(buf, stride, length, n)
+    torch.cuda.synchronize()
+    got = hexes(dig.cpu().numpy())
+    want = [hashlib.sha256(oracle.synth_object(0xB200, 11 + i, length)).hexdigest() for i in range(n)]
+    assert got == want
+    if length:
+        host = buf.cpu().numpy()
+        assert bytes(host[stride * (n - 1): stride * (n - 1) + length]) == oracle.synth_object(0xB200, 11 + n - 1, length)
+
+
+@pytest.mark.parametrize("fma", FMA_LEVELS)
+def test_fma_levels_agree_on_tma_path(hasher, fma):
+    configure(hasher, 2, fma)
+    n, length = 2000, 4096
+    buf = torch.empty(n * length, dtype=torch.uint8, device="cuda:0")
+    hasher.gen_synthetic(buf, 5, 0, n, length)
+    got = hexes(hasher.digest_device_uniform(buf, length, length, n).cpu().numpy())
+    assert got == [hashlib.sha256(oracle.synth_object(5, i, length)).hexdigest() for i in range(n)]
+
+
+# ------------------------------------------- device path, ragged offsets/lengths --
+@pytest.mark.parametrize("kernel", KERNELS)
+@pytest.mark.parametrize("align", [16, 1])
+def test_ragged_device_path_any_alignment(hasher, kernel, align):
+    configure(hasher, kernel)
+    rng = np.random.default_rng(42 + align)
+    lengths = np.concatenate([np.arange(0, 140), rng.integers(0, 1 << 14, size=400), [1 << 17, (1 << 17) + 3]])
+    rng.shuffle(lengths)
+    slots = (lengths + align - 1) // align * align + (0 if align > 1 else rng.integers(0, 3, size=lengths.size))
+    off = np.concatenate([[0], np.cumsum(slots)[:-1]]).astype(np.uint64)
+    if align == 1:
+        off += 1  # nothing is aligned
+    blob = rng.integers(0, 256, size=int(off[-1] + lengths[-1] + 64), dtype=np.uint8)
+    d_blob = torch.from_numpy(blob).cuda()
+    d_off = torch.from_numpy(off.astype(np.int64)).cuda()
+    d_len = torch.from_numpy(lengths.astype(np.int64)).cuda()
+    got = hexes(hasher.digest_device(d_blob, d_off, d_len).cpu().numpy())
+    want = [hashlib.sha256(blob[int(o):int(o) + int(n)].tobytes()).hexdigest() for o, n in zip(off, lengths)]
+    assert got == want
+    # longest-first schedule: same digests, object-major output
+    order = torch.from_numpy(np.argsort(-lengths, kind="stable").astype(np.uint32).view(np.int32)).cuda()
+    got2 = hexes(hasher.digest_device(d_blob, d_off, d_len, order=order).cpu().numpy())
+    assert got2 == want
+
+
+# ------------------------------------------------------------ host path (e2e) --
+@pytest.mark.parametrize("kernel", KERNELS)
+def test_host_path_random_lengths_property(hasher, kernel):
+    configure(hasher, kernel)
+    hasher.set_option(_ffi.OPT_WAVE_BYTES, 1 << 20)  # force many waves and buffer reuse
+    rng = np.random.default_rng(7)
+    lengths = np.concatenate([rng.integers(0, 1 << 17, size=300), [0, 0, 1, 3 << 20]])
+    objs = [rng.integers(0, 256, size=int(n), dtype=np.uint8).tobytes() for n in lengths]
+    assert hasher.hash_many(objs) == [hashlib.sha256(o).hexdigest() for o in objs]
+
+
+def test_host_path_pinned_contiguous_and_mixed_types(hasher):
+    n, length = 3000, 4096
+    host = torch.empty(n * length, dtype=torch.uint8).pin_memory()
+    host.numpy()[:] = oracle.synth_batch(9, 0, n, length)
+    off = np.arange(n, dtype=np.uint64) * length
+    dig = hasher.digest_packed(host, off, np.full(n, length, dtype=np.uint64))
+    assert hexes(dig) == [hashlib.sha256(oracle.synth_object(9, i, length)).hexdigest() for i in range(n)]
+    mixed = [b"abc", bytearray(b"defg"), memoryview(b"hij"), np.arange(10, dtype=np.uint8), b""]
+    want = [hashlib.sha256(bytes(m)).hexdigest() for m in mixed]
+    assert hasher.hash_many(mixed) == want
+    assert hasher.hash_many([]) == []
+
+
+def test_million_a_and_half_gib_message_use_64bit_length(hasher, kat):
+    assert hasher.hash_one(b"a" * 1_000_000) == kat["fips"][4]["sha256"]
+    n = (1 << 29) + 5  # bit length needs more than 32 bits
+    for kernel in (0, 2):
+        configure(hasher, kernel)
+        buf = torch.empty(n + 11, dtype=torch.uint8, device="cuda:0")
+        hasher.gen_synthetic(buf, 77, 3, 1, n, n)
+        got = hexes(hasher.digest_device_uniform(buf, n + 11 if kernel == 0 else n + 11, n, 1).cpu().numpy())[0]
+        want = hashlib.sha256(buf[:n].cpu().numpy().tobytes()).hexdigest()
+        assert got == want
+        del buf
+
+
+# ------------------------------------------ full-size, size-independent properties --
+def test_full_size_4k_config_sampled_and_cross_checked(hasher):
+    """BASELINE config 2 at full size (2^20 x 4 KiB = 4 GiB): a seeded sample of objects
+    against the oracle, and a checksum of all digests equal across the three load paths."""
+    n, length = 1 << 20, 4096
+    buf = torch.empty(n * length, dtype=torch.uint8, device="cuda:0")
+    hasher.gen_synthetic(buf, 0xB200, 0, n, length)
+    sums = []
+    for kernel in KERNELS:
+        configure(hasher, kernel)
+        dig = hasher.digest_device_uniform(buf, length, length, n)
+        torch.cuda.synchronize()
+        sums.append(hashlib.sha256(dig.cpu().numpy().tobytes()).hexdigest())
+        if kernel == 2:
+            host = dig.cpu().numpy()
+            rng = np.random.default_rng(1)
+            for i in [0, 1, 31, 32, 255, 256, n - 1] + rng.integers(0, n, size=500).tolist():
+                assert bytes(host[i]).hex() == hashlib.sha256(oracle.synth_object(0xB200, i, length)).hexdigest()
+    assert sums[0] == sums[1] == sums[2]
+
+
+def test_digests_independent_of_batch_position_and_neighbours(hasher):
+    """Idempotence / independence: an object's id does not depend on which lane or warp hashed it."""
+    rng = np.random.default_rng(3)
+    objs = [rng.integers(0, 256, size=int(n), dtype=np.uint8).tobytes() for n in rng.integers(0, 20000, size=257)]
+    a = hasher.hash_many(objs)
+    perm = rng.permutation(len(objs))
+    b = hasher.hash_many([objs[i] for i in perm])
+    assert [a[i] for i in perm] == b
+    assert hasher.hash_many(objs) == a

@@ -1,0 +1,61 @@
+"""The Storage drop-in on a B200: the reference's call patterns with real GPU hashing."""
+import asyncio
+import hashlib
+import os
+
+import pytest
+
+from bee_code_interpreter_fs_b200 import MultiGpuHasher, Storage
+
+pytestmark = pytest.mark.gpu
+
+
+def test_storage_roundtrip_like_the_reference_e2e_test(tmp_path, hasher):
+    """Shape of test_create_file_in_interpreter (reference test/e2e/test_http.py:47-85): an id
+    returned for a written file is fed back and the content round-trips."""
+
+    async def go():
+        st = Storage(str(tmp_path), hasher=hasher)
+        object_id = await st.write(b"Hello, World!")
+        assert object_id == hashlib.sha256(b"Hello, World!").hexdigest()
+        assert await st.exists(object_id)
+        assert await st.read(object_id) == b"Hello, World!"
+        async with st.reader(object_id) as r:
+            assert await r.read() == b"Hello, World!"
+        await st.delete(object_id)
+        assert not await st.exists(object_id)
+        with pytest.raises(FileNotFoundError, match=f"File not found: {object_id}"):
+            await st.read(object_id)
+
+    asyncio.run(go())
+
+
+def test_gathered_writers_share_a_gpu_batch(tmp_path, hasher):
+    async def go():
+        st = Storage(str(tmp_path), hasher=hasher, batch_window=0.05)
+        blobs = [os.urandom(1000 + 977 * i) for i in range(24)]
+
+        async def download(blob):
+            async with st.writer() as f:
+                for k in range(0, len(blob), 4096):
+                    await f.write(blob[k:k + 4096])
+            return f.hash
+
+        before = hasher.launch_count
+        ids = await asyncio.gather(*(download(b) for b in blobs))
+        assert ids == [hashlib.sha256(b).hexdigest() for b in blobs]
+        assert st.gpu_batches == 1 and hasher.launch_count == before + 1
+        many = await st.write_many(blobs)
+        assert many == ids
+        assert all((await st.verify(ids)).values())
+
+    asyncio.run(go())
+
+
+def test_multi_gpu_hasher_on_visible_devices():
+    mh = MultiGpuHasher()
+    blobs = [os.urandom(n) for n in (0, 5, 64, 100000, 3, 70000, 1 << 20)] * 3
+    assert mh.hash_many(blobs) == [hashlib.sha256(b).hexdigest() for b in blobs]
+    uniform = [os.urandom(4096) for _ in range(100)]
+    assert mh.hash_many(uniform) == [hashlib.sha256(b).hexdigest() for b in uniform]
+    mh.close()
