@@ -116,7 +116,7 @@ struct cas_ctx {
     std::string err;
     int kernel = 2;
     int fma_level = 3;
-    int ctas_per_sm = 4;
+    int ctas_per_sm = 0;  // 0 = per load path: 2 for TMA tiles, 4 for per-lane loads (measured best)
     void* encode_tiled = nullptr;  // cuTensorMapEncodeTiled, resolved through the runtime
     uint64_t wave_bytes = 256 * MiB;
     int pack_threads = 0;
@@ -211,7 +211,9 @@ cudaError_t launch_one(cas_ctx* ctx, int kernel, const cas::BatchArgs& a, cudaSt
 
 template <int FMA>
 cudaError_t launch_occ(cas_ctx* ctx, int kernel, const cas::BatchArgs& a, cudaStream_t st) {
-    switch (ctx->ctas_per_sm) {
+    int ctas = ctx->ctas_per_sm;
+    if (ctas == 0) ctas = (kernel == 2 && tma_eligible(a)) ? 2 : 4;
+    switch (ctas) {
         case 2: return launch_one<FMA, 2>(ctx, kernel, a, st);
         case 3: return launch_one<FMA, 3>(ctx, kernel, a, st);
         default: return launch_one<FMA, 4>(ctx, kernel, a, st);
@@ -358,7 +360,7 @@ int cas_create(int device, cas_ctx** out) {
     }
     if (const char* v = getenv("B200CAS_KERNEL")) ctx->kernel = std::max(0, std::min(2, atoi(v)));
     if (const char* v = getenv("B200CAS_FMA")) ctx->fma_level = std::max(0, std::min(3, atoi(v)));
-    if (const char* v = getenv("B200CAS_CTAS")) ctx->ctas_per_sm = std::max(2, std::min(4, atoi(v)));
+    if (const char* v = getenv("B200CAS_CTAS")) ctx->ctas_per_sm = atoi(v) == 0 ? 0 : std::max(2, std::min(4, atoi(v)));
     *out = ctx;
     return CAS_OK;
 }
@@ -402,7 +404,7 @@ int cas_set_option(cas_ctx* ctx, int key, int64_t v) {
             ctx->pack_threads = (int)v;
             return CAS_OK;
         case CAS_OPT_CTAS_PER_SM:
-            if (v < 2 || v > 4) return fail(ctx, CAS_E_ARG, "CAS_OPT_CTAS_PER_SM must be 2, 3 or 4");
+            if (v != 0 && (v < 2 || v > 4)) return fail(ctx, CAS_E_ARG, "CAS_OPT_CTAS_PER_SM must be 0 (auto), 2, 3 or 4");
             ctx->ctas_per_sm = (int)v;
             return CAS_OK;
     }

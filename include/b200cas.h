@@ -45,7 +45,7 @@ typedef struct cas_ctx cas_ctx;
 #define CAS_OPT_WAVE_BYTES 3   /* host path: bytes staged per wave (rounded to 1 MiB) */
 #define CAS_OPT_PACK_THREADS 4 /* host path: threads that pack objects into pinned staging */
 #define CAS_OPT_CTAS_PER_SM 5  /* resident 256-thread CTAs per SM the kernels are compiled for: 4, 3 or 2
-                                  (register budget 64, 80 or 128 per thread) */
+                                  (register budget 64, 80 or 128 per thread); 0 = best measured per load path */
 
 /* Create / destroy the per-device context (streams, staging buffers are made
  * lazily).  Replaces nothing in the reference; it is the state a
