@@ -354,8 +354,8 @@ def run_ours(args) -> None:
     try:
         with open(os.path.join(ROOT, "profiles", "dram_traffic.json")) as f:
             t = json.load(f)
-            if t.get("objects") == n and t.get("object_bytes") == length:
-                traffic = t.get("dram_bytes_per_launch")
+            if t.get("object_bytes") == length:  # per-object DRAM bytes from the ncu capture, scaled to this launch
+                traffic = t["dram_bytes_per_object"] * n
     except (OSError, ValueError):
         pass
     line = {
