@@ -14,8 +14,10 @@ OPT_KERNEL, OPT_FMA_LEVEL, OPT_WAVE_BYTES, OPT_PACK_THREADS, OPT_CTAS_PER_SM = 1
 SYMBOLS = (
     "cas_create", "cas_destroy", "cas_last_error", "cas_set_option", "cas_get_option", "cas_device_info",
     "cas_hash_host", "cas_hash_device", "cas_hash_device_uniform", "cas_gen_synthetic", "cas_int32_peak",
-    "cas_launch_count", "cas_version",
+    "cas_launch_count", "cas_version", "cas_hash_host_static",
 )
+STATIC_MAX_OBJECTS = 1024
+STATIC_MAX_BYTES = 8 << 20
 
 
 class CasError(RuntimeError):
@@ -62,6 +64,8 @@ def load() -> ctypes.CDLL:
     lib.cas_gen_synthetic.restype = ci
     lib.cas_int32_peak.argtypes = [vp, ci, ci, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double)]
     lib.cas_int32_peak.restype = ci
+    lib.cas_hash_host_static.argtypes = [ci, vp, vp, vp, u64, vp, vp]
+    lib.cas_hash_host_static.restype = ci
     lib.cas_launch_count.argtypes = [vp]
     lib.cas_launch_count.restype = u64
     lib.cas_version.argtypes = []

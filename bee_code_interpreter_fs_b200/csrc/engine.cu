@@ -655,4 +655,105 @@ int cas_hash_host(cas_ctx* ctx, const void* base, const uint64_t* off, const uin
     return CAS_OK;
 }
 
+// ---------------------------------------------------------------------------
+// cas_hash_host_static: the host-buffer path for callers that must not allocate.
+//
+// cas_hash_host stages each wave in device buffers it gets from cudaMalloc and in
+// pinned memory from cudaHostAlloc.  Some callers cannot afford that: a request
+// handler on a latency budget (cudaMalloc synchronises the whole device and can
+// stall every other stream), a process whose device memory is already handed out
+// to another allocator or capped by its operator, or code that is inside a region
+// where the runtime forbids allocation.  For them the device staging lives in the
+// file-scope array below: fixed size, part of the loaded module, held by every GPU
+// that loads this library until the process exits.
+//
+// Layout of the array: [ packed object bytes | offsets | lengths | digests ].
+// In host code `g_static_scratch` is only a stand-in symbol, not a device
+// address; the address is looked up once per device with cudaGetSymbolAddress and
+// that pointer is what the copies and the kernel get.
+static __device__ __align__(256) uint8_t
+    g_static_scratch[CAS_STATIC_MAX_BYTES + CAS_STATIC_MAX_OBJECTS * (8 + 8 + 32)];
+
+namespace {
+constexpr int STATIC_MAX_DEVICES = 64;
+std::mutex g_static_mutex;                          // one call at a time through the shared array
+uint8_t* g_static_ptr[STATIC_MAX_DEVICES] = {};     // device address of the array, per device
+
+int static_fail(int code, const char* what, cudaError_t e = cudaSuccess) { return fail(nullptr, code, what, e); }
+}  // namespace
+
+int cas_hash_host_static(int device, const void* base, const uint64_t* off, const uint64_t* len, uint64_t n,
+                         void* out32n, void* stream) {
+    if (n == 0) return CAS_OK;
+    if (!off || !len || !out32n) return static_fail(CAS_E_ARG, "cas_hash_host_static: NULL offset/length/output array");
+    if (device < 0 || device >= STATIC_MAX_DEVICES) return static_fail(CAS_E_ARG, "cas_hash_host_static: bad device index");
+    if (n > CAS_STATIC_MAX_OBJECTS) {
+        char msg[160];
+        snprintf(msg, sizeof msg, "cas_hash_host_static: %llu objects exceed the fixed scratch (at most %d per call)",
+                 (unsigned long long)n, CAS_STATIC_MAX_OBJECTS);
+        return static_fail(CAS_E_ARG, msg);
+    }
+    // Slot of every object inside the data region, 16-byte aligned (the kernel's fast path).
+    uint64_t slot[CAS_STATIC_MAX_OBJECTS], length[CAS_STATIC_MAX_OBJECTS];
+    uint64_t cursor = 0;
+    for (uint64_t i = 0; i < n; ++i) {
+        if (len[i] > CAS_STATIC_MAX_BYTES || cursor + align16(len[i]) > CAS_STATIC_MAX_BYTES) {
+            char msg[200];
+            snprintf(msg, sizeof msg,
+                     "cas_hash_host_static: batch needs more than the fixed %u-byte scratch "
+                     "(objects are padded to 16 bytes); split it or use cas_hash_host",
+                     (unsigned)CAS_STATIC_MAX_BYTES);
+            return static_fail(CAS_E_ARG, msg);
+        }
+        slot[i] = cursor;
+        length[i] = len[i];
+        cursor += align16(len[i]);
+    }
+    std::lock_guard<std::mutex> lock(g_static_mutex);
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) return static_fail(CAS_E_CUDA, "cas_hash_host_static: cudaSetDevice", e);
+    if (!g_static_ptr[device]) {
+        // Once per device, with that device current.
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_static_scratch);
+        if (e != cudaSuccess || !p) return static_fail(CAS_E_CUDA, "cas_hash_host_static: cudaGetSymbolAddress", e);
+        g_static_ptr[device] = static_cast<uint8_t*>(p);
+    }
+    uint8_t* d_data = g_static_ptr[device];
+    uint64_t* d_off = reinterpret_cast<uint64_t*>(d_data + CAS_STATIC_MAX_BYTES);
+    uint64_t* d_len = d_off + CAS_STATIC_MAX_OBJECTS;
+    uint8_t* d_dig = reinterpret_cast<uint8_t*>(d_len + CAS_STATIC_MAX_OBJECTS);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const uint8_t* hbase = static_cast<const uint8_t*>(base);
+
+    // The array keeps whatever the previous call left.  Object bytes, offsets and
+    // lengths are all rewritten below before the kernel reads them; the digest
+    // slots are the one thing that must not carry over, so they start at zero.
+    e = cudaMemsetAsync(d_dig, 0, n * 32, st);
+    if (e != cudaSuccess) return static_fail(CAS_E_CUDA, "cas_hash_host_static: cudaMemsetAsync", e);
+    for (uint64_t i = 0; i < n; ++i) {
+        if (!length[i]) continue;
+        e = cudaMemcpyAsync(d_data + slot[i], hbase + off[i], length[i], cudaMemcpyHostToDevice, st);
+        if (e != cudaSuccess) return static_fail(CAS_E_CUDA, "cas_hash_host_static: copy of an object to the device", e);
+    }
+    e = cudaMemcpyAsync(d_off, slot, n * 8, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_len, length, n * 8, cudaMemcpyHostToDevice, st);
+    if (e != cudaSuccess) return static_fail(CAS_E_CUDA, "cas_hash_host_static: copy of offsets/lengths", e);
+    cas::BatchArgs a{};
+    a.base = d_data;
+    a.off = d_off;
+    a.len = d_len;
+    a.n = n;
+    a.out = d_dig;
+    a.one = 1u;
+    a.zero = 0u;
+    cas::kernel_ldg<3, THREADS, 4><<<(unsigned)((n + THREADS - 1) / THREADS), THREADS, 0, st>>>(a);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return static_fail(CAS_E_CUDA, "cas_hash_host_static: kernel launch", e);
+    e = cudaMemcpyAsync(out32n, d_dig, n * 32, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) return static_fail(CAS_E_CUDA, "cas_hash_host_static: digest copy / synchronize", e);
+    return CAS_OK;
+}
+
 }  // extern "C"

@@ -98,6 +98,37 @@ int cas_gen_synthetic(cas_ctx* ctx, void* d_dst, uint64_t seed, uint64_t first_o
  * Returns thread-level instructions per second and the kernel time. */
 int cas_int32_peak(cas_ctx* ctx, int mode, int steps, double* lane_ops_per_s, double* ms);
 
+/*
+ * No counterpart in the reference: a variant of cas_hash_host that allocates nothing.
+ *
+ * cas_hash_host gets its device and pinned staging from cudaMalloc/cudaHostAlloc.  A caller
+ * that cannot allocate -- a request handler that must not take cudaMalloc's device-wide
+ * synchronisation, a process whose GPU memory is fully owned by another allocator or capped
+ * by its operator, code running where the runtime forbids allocation -- uses this entry
+ * point instead: the device staging is a fixed array inside the library
+ * (CAS_STATIC_MAX_BYTES + 48 bytes per object slot, about 8.05 MiB), resident on every GPU
+ * that loads the library until the process exits.  No context is needed.
+ *
+ * Same inputs and outputs as cas_hash_host (host memory; base may be NULL for absolute
+ * addresses), plus the device index and a cudaStream_t (NULL = default stream).  The call
+ * is synchronous.  Limits: at most CAS_STATIC_MAX_OBJECTS objects and CAS_STATIC_MAX_BYTES
+ * bytes per call, counting each object rounded up to 16 bytes; larger batches are rejected
+ * with CAS_E_ARG and a message saying so (cas_last_error(NULL)) -- split them, or use
+ * cas_hash_host.  It calls no cudaMalloc, cudaFree, cudaHostAlloc or any other allocating
+ * routine, creates no stream or event, and copies straight from the caller's memory.
+ *
+ * The first call on a device looks up the array's device address (cudaGetSymbolAddress);
+ * make that first call before starting any stream capture.  All calls on a device share
+ * the one array, which still holds the previous call's bytes: everything the kernel reads
+ * is rewritten first and the digest slots are zeroed first.  Calls are serialised by a
+ * lock inside the library, because two calls in flight on the same GPU would overwrite
+ * each other's staging and race.
+ */
+#define CAS_STATIC_MAX_OBJECTS 1024
+#define CAS_STATIC_MAX_BYTES (8u << 20)
+int cas_hash_host_static(int device, const void* base, const uint64_t* off, const uint64_t* len, uint64_t n,
+                         void* out32n, void* stream);
+
 /* Number of kernels this context has launched since creation. */
 uint64_t cas_launch_count(const cas_ctx* ctx);
 
