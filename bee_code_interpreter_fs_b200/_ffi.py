@@ -8,7 +8,7 @@ from ._build import LIB_PATH
 
 CAS_OK = 0
 CAS_E_CUDA, CAS_E_ARG, CAS_E_NOMEM, CAS_E_NODEVICE = -1, -2, -3, -4
-OPT_KERNEL, OPT_FMA_LEVEL, OPT_WAVE_BYTES, OPT_PACK_THREADS, OPT_CTAS_PER_SM = 1, 2, 3, 4, 5
+OPT_KERNEL, OPT_FMA_LEVEL, OPT_WAVE_BYTES, OPT_PACK_THREADS, OPT_CTAS_PER_SM, OPT_ARENA_BYTES = 1, 2, 3, 4, 5, 6
 
 # Every symbol include/b200cas.h declares (tests check the library exports them all).
 SYMBOLS = (

@@ -4,11 +4,14 @@
 // (/root/reference/src/code_interpreter/services/storage.py:44-63): take a batch
 // of objects, return their SHA-256 object ids.  Device side: csrc/sha256_batch.cuh.
 //
-// Host-buffer pipeline (cas_hash_host): objects are ordered longest-first, cut
-// into waves, packed 16-byte aligned into pinned staging by a few host threads
-// (or DMA'd straight from the caller's memory when that is pinned and laid out
-// contiguously), copied with cudaMemcpyAsync on a copy stream while the previous
-// wave is hashed on a compute stream; 32-byte digests come back per wave.
+// Host-buffer pipeline (cas_hash_host): objects are ordered longest-first and laid
+// out 16-byte aligned in a device arena; the arena's byte range is cut into chunks
+// (independent of object boundaries) that are packed into pinned staging by a few
+// host threads -- or DMA'd straight from the caller's memory when that is pinned
+// and contiguous -- and copied with cudaMemcpyAsync on a copy stream.  As soon as
+// the last byte of a group of objects has landed, a kernel for that group starts
+// on one of several compute streams, so long serial chains from early chunks
+// overlap both later copies and later kernels.  Digests come back once at the end.
 #include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -32,7 +35,6 @@
 
 namespace {
 
-constexpr int NBUF = 3;
 constexpr uint64_t MiB = 1ull << 20;
 
 std::string g_create_error;
@@ -92,18 +94,14 @@ private:
     int pending_;
 };
 
-struct WaveBuf {
-    uint8_t* h_stage = nullptr;  // pinned, data_cap bytes
-    uint8_t* d_data = nullptr;   // device, data_cap bytes
-    uint64_t data_cap = 0;
-    uint64_t* h_meta = nullptr;  // pinned, 2*obj_cap words: offsets then lengths
-    uint64_t* d_meta = nullptr;
-    uint8_t* h_dig = nullptr;    // pinned, 32*obj_cap
-    uint8_t* d_dig = nullptr;
-    uint64_t obj_cap = 0;
-    cudaEvent_t ev_done = nullptr;
-    bool busy = false;
-    uint64_t first = 0, count = 0;  // slice of the schedule this buffer holds
+constexpr int NSTG = 3;   // pinned staging buffers in flight
+constexpr int NCOMP = 4;  // compute streams
+
+struct Stage {
+    uint8_t* h = nullptr;  // pinned staging
+    uint64_t cap = 0;
+    cudaEvent_t ev = nullptr;  // recorded after the chunk's last H2D copy
+    bool used = false;
 };
 
 }  // namespace
@@ -121,9 +119,19 @@ struct cas_ctx {
     uint64_t wave_bytes = 256 * MiB;
     int pack_threads = 0;
     uint64_t launches = 0;
-    cudaStream_t s_copy = nullptr, s_comp = nullptr;
-    cudaEvent_t ev_h2d[NBUF] = {nullptr, nullptr, nullptr};
-    WaveBuf buf[NBUF];
+    uint64_t arena_max = 32ull << 30;  // device bytes the host path may hold (two halves)
+    cudaStream_t s_copy = nullptr;
+    cudaStream_t s_comp[NCOMP] = {};
+    cudaEvent_t ev_epoch[2][NCOMP] = {};  // kernels of the epoch that last used an arena half
+    cudaEvent_t ev_join[NCOMP] = {};
+    Stage stage[NSTG];
+    uint8_t* d_arena = nullptr;
+    uint64_t arena_cap = 0;
+    uint64_t* h_meta = nullptr;  // pinned: offsets[n] then lengths[n], schedule order
+    uint64_t* d_meta = nullptr;
+    uint8_t* h_dig = nullptr;    // pinned: 32 n
+    uint8_t* d_dig = nullptr;
+    uint64_t obj_cap = 0;
     PackPool* pool = nullptr;
     uint32_t* d_sink = nullptr;
 };
@@ -230,7 +238,8 @@ int launch_batch(cas_ctx* ctx, cas::BatchArgs a, cudaStream_t st) {
         case 0: e = launch_occ<0>(ctx, ctx->kernel, a, st); break;
         case 1: e = launch_occ<1>(ctx, ctx->kernel, a, st); break;
         case 2: e = launch_occ<2>(ctx, ctx->kernel, a, st); break;
-        default: e = launch_occ<3>(ctx, ctx->kernel, a, st); break;
+        case 3: e = launch_occ<3>(ctx, ctx->kernel, a, st); break;
+        default: e = launch_occ<4>(ctx, ctx->kernel, a, st); break;
     }
     if (e != cudaSuccess) return fail(ctx, CAS_E_CUDA, "sha256 batch kernel launch", e);
     ++ctx->launches;
@@ -240,61 +249,37 @@ int launch_batch(cas_ctx* ctx, cas::BatchArgs a, cudaStream_t st) {
 inline uint64_t align16(uint64_t x) { return (x + 15u) & ~15ull; }
 inline uint64_t nblocks(uint64_t len) { return (len + 9 + 63) / 64; }
 
-void free_buf(WaveBuf& b) {
-    if (b.h_stage) cudaFreeHost(b.h_stage);
-    if (b.d_data) cudaFree(b.d_data);
-    if (b.h_meta) cudaFreeHost(b.h_meta);
-    if (b.d_meta) cudaFree(b.d_meta);
-    if (b.h_dig) cudaFreeHost(b.h_dig);
-    if (b.d_dig) cudaFree(b.d_dig);
-    if (b.ev_done) cudaEventDestroy(b.ev_done);
-    b = WaveBuf();
+void free_host_path(cas_ctx* c) {
+    for (auto& st : c->stage) {
+        if (st.h) cudaFreeHost(st.h);
+        if (st.ev) cudaEventDestroy(st.ev);
+        st = Stage();
+    }
+    if (c->d_arena) cudaFree(c->d_arena);
+    if (c->h_meta) cudaFreeHost(c->h_meta);
+    if (c->d_meta) cudaFree(c->d_meta);
+    if (c->h_dig) cudaFreeHost(c->h_dig);
+    if (c->d_dig) cudaFree(c->d_dig);
+    c->d_arena = nullptr; c->arena_cap = 0;
+    c->h_meta = nullptr; c->d_meta = nullptr; c->h_dig = nullptr; c->d_dig = nullptr; c->obj_cap = 0;
+    for (auto& half : c->ev_epoch)
+        for (auto& ev : half)
+            if (ev) { cudaEventDestroy(ev); ev = nullptr; }
+    for (auto& ev : c->ev_join)
+        if (ev) { cudaEventDestroy(ev); ev = nullptr; }
 }
 
-int ensure_buf(cas_ctx* ctx, WaveBuf& b, uint64_t data_bytes, uint64_t objs) {
-    if (!b.ev_done) CU(cudaEventCreateWithFlags(&b.ev_done, cudaEventDisableTiming));
-    if (data_bytes > b.data_cap) {
-        if (b.h_stage) cudaFreeHost(b.h_stage);
-        if (b.d_data) cudaFree(b.d_data);
-        b.h_stage = nullptr; b.d_data = nullptr; b.data_cap = 0;
-        const uint64_t cap = (data_bytes + MiB - 1) & ~(MiB - 1);
-        if (cudaHostAlloc((void**)&b.h_stage, cap, cudaHostAllocDefault) != cudaSuccess) {
-            cudaGetLastError();
-            return fail(ctx, CAS_E_NOMEM, "pinned staging allocation failed");
-        }
-        if (cudaMalloc((void**)&b.d_data, cap) != cudaSuccess) {
-            cudaGetLastError();
-            return fail(ctx, CAS_E_NOMEM, "device wave buffer allocation failed");
-        }
-        b.data_cap = cap;
-    }
-    if (objs > b.obj_cap) {
-        if (b.h_meta) cudaFreeHost(b.h_meta);
-        if (b.d_meta) cudaFree(b.d_meta);
-        if (b.h_dig) cudaFreeHost(b.h_dig);
-        if (b.d_dig) cudaFree(b.d_dig);
-        b.h_meta = nullptr; b.d_meta = nullptr; b.h_dig = nullptr; b.d_dig = nullptr; b.obj_cap = 0;
-        const uint64_t cap = std::max<uint64_t>(1024, objs + objs / 4);
-        if (cudaHostAlloc((void**)&b.h_meta, cap * 16, cudaHostAllocDefault) != cudaSuccess ||
-            cudaHostAlloc((void**)&b.h_dig, cap * 32, cudaHostAllocDefault) != cudaSuccess) {
-            cudaGetLastError();
-            return fail(ctx, CAS_E_NOMEM, "pinned metadata allocation failed");
-        }
-        if (cudaMalloc((void**)&b.d_meta, cap * 16) != cudaSuccess ||
-            cudaMalloc((void**)&b.d_dig, cap * 32) != cudaSuccess) {
-            cudaGetLastError();
-            return fail(ctx, CAS_E_NOMEM, "device metadata allocation failed");
-        }
-        b.obj_cap = cap;
-    }
-    return CAS_OK;
-}
-
-int ensure_streams(cas_ctx* ctx) {
+// Grow-only resources of the host path: nothing is allocated per call once the
+// largest batch shape has been seen.
+int ensure_host_path(cas_ctx* ctx, uint64_t arena_bytes, uint64_t stage_bytes, uint64_t objs) {
     if (!ctx->s_copy) CU(cudaStreamCreateWithFlags(&ctx->s_copy, cudaStreamNonBlocking));
-    if (!ctx->s_comp) CU(cudaStreamCreateWithFlags(&ctx->s_comp, cudaStreamNonBlocking));
-    for (int i = 0; i < NBUF; ++i)
-        if (!ctx->ev_h2d[i]) CU(cudaEventCreateWithFlags(&ctx->ev_h2d[i], cudaEventDisableTiming));
+    for (auto& st : ctx->s_comp)
+        if (!st) CU(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+    for (auto& half : ctx->ev_epoch)
+        for (auto& ev : half)
+            if (!ev) CU(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    for (auto& ev : ctx->ev_join)
+        if (!ev) CU(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
     if (!ctx->pool) {
         int n = ctx->pack_threads;
         if (n <= 0) {
@@ -302,6 +287,48 @@ int ensure_streams(cas_ctx* ctx) {
             n = std::max(1, std::min(n, 16));
         }
         ctx->pool = new PackPool(n);
+    }
+    if (arena_bytes > ctx->arena_cap) {
+        if (ctx->d_arena) cudaFree(ctx->d_arena);
+        ctx->d_arena = nullptr; ctx->arena_cap = 0;
+        const uint64_t cap = (arena_bytes + 2 * MiB - 1) & ~(2 * MiB - 1);
+        if (cudaMalloc((void**)&ctx->d_arena, cap) != cudaSuccess) {
+            cudaGetLastError();
+            return fail(ctx, CAS_E_NOMEM, "device arena allocation failed");
+        }
+        ctx->arena_cap = cap;
+    }
+    for (auto& st : ctx->stage) {
+        if (!st.ev) CU(cudaEventCreateWithFlags(&st.ev, cudaEventDisableTiming));
+        if (stage_bytes > st.cap) {
+            if (st.h) cudaFreeHost(st.h);
+            st.h = nullptr; st.cap = 0;
+            const uint64_t cap = (stage_bytes + MiB - 1) & ~(MiB - 1);
+            if (cudaHostAlloc((void**)&st.h, cap, cudaHostAllocDefault) != cudaSuccess) {
+                cudaGetLastError();
+                return fail(ctx, CAS_E_NOMEM, "pinned staging allocation failed");
+            }
+            st.cap = cap;
+        }
+    }
+    if (objs > ctx->obj_cap) {
+        if (ctx->h_meta) cudaFreeHost(ctx->h_meta);
+        if (ctx->d_meta) cudaFree(ctx->d_meta);
+        if (ctx->h_dig) cudaFreeHost(ctx->h_dig);
+        if (ctx->d_dig) cudaFree(ctx->d_dig);
+        ctx->h_meta = nullptr; ctx->d_meta = nullptr; ctx->h_dig = nullptr; ctx->d_dig = nullptr; ctx->obj_cap = 0;
+        const uint64_t cap = std::max<uint64_t>(1024, objs + objs / 4);
+        if (cudaHostAlloc((void**)&ctx->h_meta, cap * 16, cudaHostAllocDefault) != cudaSuccess ||
+            cudaHostAlloc((void**)&ctx->h_dig, cap * 32, cudaHostAllocDefault) != cudaSuccess) {
+            cudaGetLastError();
+            return fail(ctx, CAS_E_NOMEM, "pinned metadata allocation failed");
+        }
+        if (cudaMalloc((void**)&ctx->d_meta, cap * 16) != cudaSuccess ||
+            cudaMalloc((void**)&ctx->d_dig, cap * 32) != cudaSuccess) {
+            cudaGetLastError();
+            return fail(ctx, CAS_E_NOMEM, "device metadata allocation failed");
+        }
+        ctx->obj_cap = cap;
     }
     return CAS_OK;
 }
@@ -359,7 +386,7 @@ int cas_create(int device, cas_ctx** out) {
         return fail(nullptr, CAS_E_CUDA, "cuTensorMapEncodeTiled not available from this driver", e);
     }
     if (const char* v = getenv("B200CAS_KERNEL")) ctx->kernel = std::max(0, std::min(2, atoi(v)));
-    if (const char* v = getenv("B200CAS_FMA")) ctx->fma_level = std::max(0, std::min(3, atoi(v)));
+    if (const char* v = getenv("B200CAS_FMA")) ctx->fma_level = std::max(0, std::min(4, atoi(v)));
     if (const char* v = getenv("B200CAS_CTAS")) ctx->ctas_per_sm = atoi(v) == 0 ? 0 : std::max(2, std::min(4, atoi(v)));
     *out = ctx;
     return CAS_OK;
@@ -368,12 +395,10 @@ int cas_create(int device, cas_ctx** out) {
 void cas_destroy(cas_ctx* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
-    if (ctx->s_comp) cudaStreamSynchronize(ctx->s_comp);
-    if (ctx->s_copy) cudaStreamSynchronize(ctx->s_copy);
-    for (auto& b : ctx->buf) free_buf(b);
-    for (auto& ev : ctx->ev_h2d)
-        if (ev) cudaEventDestroy(ev);
-    if (ctx->s_comp) cudaStreamDestroy(ctx->s_comp);
+    cudaDeviceSynchronize();
+    free_host_path(ctx);
+    for (auto& st : ctx->s_comp)
+        if (st) cudaStreamDestroy(st);
     if (ctx->s_copy) cudaStreamDestroy(ctx->s_copy);
     if (ctx->d_sink) cudaFree(ctx->d_sink);
     delete ctx->pool;
@@ -388,7 +413,7 @@ int cas_set_option(cas_ctx* ctx, int key, int64_t v) {
             ctx->kernel = (int)v;
             return CAS_OK;
         case CAS_OPT_FMA_LEVEL:
-            if (v < 0 || v > 3) return fail(ctx, CAS_E_ARG, "CAS_OPT_FMA_LEVEL must be 0..3");
+            if (v < 0 || v > 4) return fail(ctx, CAS_E_ARG, "CAS_OPT_FMA_LEVEL must be 0..4");
             ctx->fma_level = (int)v;
             return CAS_OK;
         case CAS_OPT_WAVE_BYTES:
@@ -402,6 +427,10 @@ int cas_set_option(cas_ctx* ctx, int key, int64_t v) {
                 ctx->pool = nullptr;
             }
             ctx->pack_threads = (int)v;
+            return CAS_OK;
+        case CAS_OPT_ARENA_BYTES:
+            if (v < (int64_t)(64 * MiB)) return fail(ctx, CAS_E_ARG, "CAS_OPT_ARENA_BYTES must be >= 64 MiB");
+            ctx->arena_max = (uint64_t)v;
             return CAS_OK;
         case CAS_OPT_CTAS_PER_SM:
             if (v != 0 && (v < 2 || v > 4)) return fail(ctx, CAS_E_ARG, "CAS_OPT_CTAS_PER_SM must be 0 (auto), 2, 3 or 4");
@@ -419,6 +448,7 @@ int cas_get_option(const cas_ctx* ctx, int key, int64_t* v) {
         case CAS_OPT_WAVE_BYTES: *v = (int64_t)ctx->wave_bytes; return CAS_OK;
         case CAS_OPT_PACK_THREADS: *v = ctx->pool ? ctx->pool->size() : ctx->pack_threads; return CAS_OK;
         case CAS_OPT_CTAS_PER_SM: *v = ctx->ctas_per_sm; return CAS_OK;
+        case CAS_OPT_ARENA_BYTES: *v = (int64_t)ctx->arena_max; return CAS_OK;
     }
     return CAS_E_ARG;
 }
@@ -487,7 +517,7 @@ int cas_gen_synthetic(cas_ctx* ctx, void* d_dst, uint64_t seed, uint64_t first_o
 
 int cas_int32_peak(cas_ctx* ctx, int mode, int steps, double* lane_ops_per_s, double* ms_out) {
     if (!ctx) return CAS_E_ARG;
-    if (mode < 0 || mode > 4 || steps < cas::PEAK_UNROLL) return fail(ctx, CAS_E_ARG, "cas_int32_peak: bad mode/steps");
+    if (mode < 0 || mode > 6 || steps < cas::PEAK_UNROLL) return fail(ctx, CAS_E_ARG, "cas_int32_peak: bad mode/steps");
     CU(cudaSetDevice(ctx->device));
     if (!ctx->d_sink) CU(cudaMalloc((void**)&ctx->d_sink, 256));
     steps -= steps % cas::PEAK_UNROLL;
@@ -503,7 +533,9 @@ int cas_int32_peak(cas_ctx* ctx, int mode, int steps, double* lane_ops_per_s, do
             case 1: cas::kernel_peak<1><<<grid, cas::PEAK_THREADS>>>(ctx->d_sink, steps, 1u, 12345u + rep); break;
             case 2: cas::kernel_peak<2><<<grid, cas::PEAK_THREADS>>>(ctx->d_sink, steps, 1u, 12345u + rep); break;
             case 3: cas::kernel_peak<3><<<grid, cas::PEAK_THREADS>>>(ctx->d_sink, steps, 1u, 12345u + rep); break;
-            default: cas::kernel_peak<4><<<grid, cas::PEAK_THREADS>>>(ctx->d_sink, steps, 1u, 12345u + rep); break;
+            case 4: cas::kernel_peak<4><<<grid, cas::PEAK_THREADS>>>(ctx->d_sink, steps, 1u, 12345u + rep); break;
+            case 5: cas::kernel_peak<5><<<grid, cas::PEAK_THREADS>>>(ctx->d_sink, steps, 1u, 12345u + rep); break;
+            default: cas::kernel_peak<6><<<grid, cas::PEAK_THREADS>>>(ctx->d_sink, steps, 1u, 12345u + rep); break;
         }
         CU(cudaGetLastError());
         CU(cudaEventRecord(e1, 0));
@@ -528,19 +560,11 @@ int cas_hash_host(cas_ctx* ctx, const void* base, const uint64_t* off, const uin
     if (!off || !len || !out32n) return fail(ctx, CAS_E_ARG, "cas_hash_host: NULL offset/length/output array");
     if (n > 0xFFFFFFFFull) return fail(ctx, CAS_E_ARG, "cas_hash_host: more than 2^32-1 objects in one call");
     CU(cudaSetDevice(ctx->device));
-    int rc = ensure_streams(ctx);
-    if (rc) return rc;
     const uint8_t* hbase = static_cast<const uint8_t*>(base);
     uint8_t* out = static_cast<uint8_t*>(out32n);
-    // A previous call that failed half-way may have left waves in flight.
-    for (auto& b : ctx->buf)
-        if (b.busy) {
-            cudaEventSynchronize(b.ev_done);
-            b.busy = false;
-        }
 
     // Schedule: longest first when lengths differ, so that the 32 lanes of a warp
-    // carry messages of (nearly) equal block counts and big objects start early.
+    // carry messages of (nearly) equal block counts and the long chains start early.
     uint64_t total = 0, maxlen = 0;
     bool uniform = true;
     for (uint64_t i = 0; i < n; ++i) {
@@ -554,104 +578,129 @@ int cas_hash_host(cas_ctx* ctx, const void* base, const uint64_t* off, const uin
         std::stable_sort(order.begin(), order.end(),
                          [&](uint32_t a, uint32_t b) { return nblocks(len[a]) > nblocks(len[b]); });
 
-    // Wave size: small batches are cut finer so that copy and hash still overlap.
-    uint64_t wave_cap = std::min<uint64_t>(ctx->wave_bytes, std::max<uint64_t>(8 * MiB, (total / 8 + MiB - 1) & ~(MiB - 1)));
-    wave_cap = std::max<uint64_t>(wave_cap, align16(maxlen));
-    const uint64_t wave_objs = 1ull << 22;
+    // Chunk (copy granule) and arena sizes.  Small batches are cut finer so that copy
+    // and hash still overlap; the arena has two halves so that the copies of one epoch
+    // run while the kernels of the previous one finish.
+    uint64_t chunk = std::min<uint64_t>(ctx->wave_bytes, std::max<uint64_t>(8 * MiB, (total / 8 + MiB - 1) & ~(MiB - 1)));
+    uint64_t half = std::max<uint64_t>(std::min<uint64_t>(ctx->arena_max / 2, (total + MiB - 1) & ~(MiB - 1)),
+                                       std::max<uint64_t>(align16(maxlen), 16));
+    half = (half + 255) & ~255ull;
+    const bool one_epoch = total <= half;
+    int rc = ensure_host_path(ctx, one_epoch ? half : 2 * half, chunk, n);
+    if (rc) return rc;
     const bool pinned_src = host_ptr_is_pinned(hbase);
 
-    auto drain = [&](WaveBuf& b) -> int {
-        if (!b.busy) return CAS_OK;
-        CU(cudaEventSynchronize(b.ev_done));
-        for (uint64_t k = 0; k < b.count; ++k) memcpy(out + 32ull * order[b.first + k], b.h_dig + 32ull * k, 32);
-        b.busy = false;
-        return CAS_OK;
-    };
-
-    uint64_t pos = 0;
-    int w = 0;
-    while (pos < n) {
-        // Cut the next wave.
-        uint64_t cnt = 0, bytes = 0;
-        while (pos + cnt < n && cnt < wave_objs) {
-            const uint64_t need = align16(len[order[pos + cnt]]);
-            if (cnt && bytes + need > wave_cap) break;
-            bytes += need;
-            ++cnt;
-        }
-        WaveBuf& b = ctx->buf[w % NBUF];
-        if ((rc = drain(b))) return rc;
-        if ((rc = ensure_buf(ctx, b, std::max<uint64_t>(bytes, 16), cnt))) return rc;
-        b.first = pos;
-        b.count = cnt;
-        uint64_t* h_off = b.h_meta;
-        uint64_t* h_len = b.h_meta + cnt;
+    // Device layout in schedule order; epochs are runs of objects that fit one arena half.
+    uint64_t* h_off = ctx->h_meta;
+    uint64_t* h_len = ctx->h_meta + n;
+    std::vector<uint64_t> epoch_first;  // schedule index where each epoch starts
+    {
         uint64_t cursor = 0;
-        for (uint64_t k = 0; k < cnt; ++k) {
-            const uint64_t L = len[order[pos + k]];
-            h_off[k] = cursor;
-            h_len[k] = L;
-            cursor += align16(L);
-        }
-        // Direct DMA from the caller's pinned memory when the wave is a few
-        // contiguous runs whose objects all stay 16-byte aligned; else pack.
-        bool direct = false;
-        std::vector<std::pair<uint64_t, uint64_t>> runs;  // (first k, byte count)
-        if (pinned_src) {
-            direct = true;
-            uint64_t k = 0;
-            while (k < cnt && direct) {
-                uint64_t k0 = k, run_bytes = align16(len[order[pos + k]]);
-                const uint64_t src0 = off[order[pos + k]];
-                ++k;
-                while (k < cnt && off[order[pos + k]] == src0 + run_bytes) {
-                    run_bytes += align16(len[order[pos + k]]);
-                    ++k;
-                }
-                // The last object of a run may be shorter than its aligned slot.
-                const uint64_t last = order[pos + k - 1];
-                runs.emplace_back(k0, run_bytes - (align16(len[last]) - len[last]));
-                if (runs.size() > 64) direct = false;
+        epoch_first.push_back(0);
+        for (uint64_t k = 0; k < n; ++k) {
+            const uint64_t need = align16(len[order[k]]);
+            if (cursor + need > half) {
+                epoch_first.push_back(k);
+                cursor = 0;
             }
+            h_off[k] = cursor;
+            h_len[k] = len[order[k]];
+            cursor += need;
         }
-        if (direct) {
-            for (auto& r : runs)
-                if (r.second)
-                    CU(cudaMemcpyAsync(b.d_data + h_off[r.first], hbase + off[order[pos + r.first]], r.second,
-                                       cudaMemcpyHostToDevice, ctx->s_copy));
-        } else {
-            const int T = ctx->pool->size();
-            const uint64_t share = (bytes + T - 1) / (uint64_t)T;
-            ctx->pool->run([&](int t) {
-                const uint64_t lo = share * (uint64_t)t, hi = std::min(bytes, lo + share);
-                if (lo >= hi) return;
-                // first object whose slot starts at or after lo
-                uint64_t k = std::lower_bound(h_off, h_off + cnt, lo) - h_off;
-                for (; k < cnt && h_off[k] < hi; ++k) {
-                    const uint64_t o = order[pos + k];
-                    if (h_len[k]) memcpy(b.h_stage + h_off[k], hbase + off[o], h_len[k]);
-                }
-            });
-            if (bytes) CU(cudaMemcpyAsync(b.d_data, b.h_stage, bytes, cudaMemcpyHostToDevice, ctx->s_copy));
-        }
-        CU(cudaMemcpyAsync(b.d_meta, b.h_meta, cnt * 16, cudaMemcpyHostToDevice, ctx->s_copy));
-        CU(cudaEventRecord(ctx->ev_h2d[w % NBUF], ctx->s_copy));
-        CU(cudaStreamWaitEvent(ctx->s_comp, ctx->ev_h2d[w % NBUF], 0));
-        cas::BatchArgs a{};
-        a.base = b.d_data;
-        a.off = b.d_meta;
-        a.len = b.d_meta + cnt;
-        a.n = cnt;
-        a.out = b.d_dig;
-        if ((rc = launch_batch(ctx, a, ctx->s_comp))) return rc;
-        CU(cudaMemcpyAsync(b.h_dig, b.d_dig, cnt * 32, cudaMemcpyDeviceToHost, ctx->s_comp));
-        CU(cudaEventRecord(b.ev_done, ctx->s_comp));
-        b.busy = true;
-        pos += cnt;
-        ++w;
+        epoch_first.push_back(n);
     }
-    for (int i = 0; i < NBUF; ++i)
-        if ((rc = drain(ctx->buf[(w + i) % NBUF]))) return rc;
+    CU(cudaMemcpyAsync(ctx->d_meta, h_off, n * 8, cudaMemcpyHostToDevice, ctx->s_copy));
+    CU(cudaMemcpyAsync(ctx->d_meta + n, h_len, n * 8, cudaMemcpyHostToDevice, ctx->s_copy));
+    for (auto& st : ctx->stage) st.used = false;
+
+    struct Piece { const uint8_t* src; uint64_t dst; uint64_t bytes; };
+    std::vector<Piece> pieces;
+    uint64_t chunk_no = 0, launch_no = 0;
+    for (size_t e = 0; e + 1 < epoch_first.size(); ++e) {
+        const uint64_t k0 = epoch_first[e], k1 = epoch_first[e + 1];
+        uint8_t* d_base = ctx->d_arena + (one_epoch ? 0 : (e & 1) * half);
+        if (e >= 2)  // this half was last read by the kernels of epoch e-2
+            for (int i = 0; i < NCOMP; ++i) CU(cudaStreamWaitEvent(ctx->s_copy, ctx->ev_epoch[e & 1][i], 0));
+        const uint64_t bytes = h_off[k1 - 1] + align16(h_len[k1 - 1]);
+        uint64_t kp = k0;       // first object that still has bytes to copy
+        uint64_t klaunch = k0;  // first object not yet handed to a kernel
+        for (uint64_t c0 = 0; c0 < bytes || klaunch < k1; c0 += chunk) {
+            const uint64_t c1 = std::min(bytes, c0 + chunk);
+            Stage& sg = ctx->stage[chunk_no % NSTG];
+            // Pieces of objects that fall into [c0, c1), merged when contiguous on both sides.
+            pieces.clear();
+            while (kp < k1 && h_off[kp] + h_len[kp] <= c0) ++kp;
+            for (uint64_t k = kp; k < k1 && h_off[k] < c1; ++k) {
+                const uint64_t lo = std::max(h_off[k], c0), hi = std::min(h_off[k] + h_len[k], c1);
+                if (lo >= hi) continue;
+                const uint8_t* src = hbase + off[order[k]] + (lo - h_off[k]);
+                if (!pieces.empty() && pieces.back().src + pieces.back().bytes == src &&
+                    pieces.back().dst + pieces.back().bytes == lo)
+                    pieces.back().bytes += hi - lo;
+                else
+                    pieces.push_back({src, lo, hi - lo});
+            }
+            if (c1 > c0) {
+                if (pinned_src && pieces.size() <= 64) {
+                    for (auto& pc : pieces)
+                        CU(cudaMemcpyAsync(d_base + pc.dst, pc.src, pc.bytes, cudaMemcpyHostToDevice, ctx->s_copy));
+                } else if (!pieces.empty()) {
+                    if (sg.used) CU(cudaEventSynchronize(sg.ev));  // its previous H2D has left the staging
+                    const int T = ctx->pool->size();
+                    const uint64_t span = c1 - c0, share = ((span + T - 1) / (uint64_t)T + 63) & ~63ull;
+                    uint8_t* stage = sg.h;
+                    const Piece* pv = pieces.data();
+                    const size_t np = pieces.size();
+                    ctx->pool->run([&](int t) {
+                        const uint64_t lo = c0 + share * (uint64_t)t, hi = std::min(c1, lo + share);
+                        if (lo >= hi) return;
+                        // first piece that ends after lo
+                        size_t i = std::partition_point(pv, pv + np, [&](const Piece& q) { return q.dst + q.bytes <= lo; }) - pv;
+                        for (; i < np && pv[i].dst < hi; ++i) {
+                            const uint64_t a = std::max(pv[i].dst, lo), b = std::min(pv[i].dst + pv[i].bytes, hi);
+                            memcpy(stage + (a - c0), pv[i].src + (a - pv[i].dst), b - a);
+                        }
+                    });
+                    CU(cudaMemcpyAsync(d_base + c0, stage, span, cudaMemcpyHostToDevice, ctx->s_copy));
+                    sg.used = true;
+                }
+            }
+            CU(cudaEventRecord(sg.ev, ctx->s_copy));
+            ++chunk_no;
+            // Objects whose last byte is now on the device.
+            uint64_t kend = klaunch;
+            while (kend < k1 && h_off[kend] + h_len[kend] <= c1) ++kend;
+            if (c1 >= bytes) kend = k1;
+            if (kend > klaunch) {
+                cudaStream_t cs = ctx->s_comp[launch_no % NCOMP];
+                CU(cudaStreamWaitEvent(cs, sg.ev, 0));
+                cas::BatchArgs a{};
+                a.base = d_base;
+                a.off = ctx->d_meta + klaunch;
+                a.len = ctx->d_meta + n + klaunch;
+                a.n = kend - klaunch;
+                a.out = ctx->d_dig + 32ull * klaunch;
+                if ((rc = launch_batch(ctx, a, cs))) return rc;
+                ++launch_no;
+                klaunch = kend;
+            }
+            if (c1 >= bytes) break;
+        }
+        for (int i = 0; i < NCOMP; ++i) CU(cudaEventRecord(ctx->ev_epoch[e & 1][i], ctx->s_comp[i]));
+    }
+    // Join the compute streams, bring the digests back, restore the caller's order.
+    for (int i = 1; i < NCOMP; ++i) {
+        CU(cudaEventRecord(ctx->ev_join[i], ctx->s_comp[i]));
+        CU(cudaStreamWaitEvent(ctx->s_comp[0], ctx->ev_join[i], 0));
+    }
+    CU(cudaMemcpyAsync(ctx->h_dig, ctx->d_dig, n * 32, cudaMemcpyDeviceToHost, ctx->s_comp[0]));
+    CU(cudaStreamSynchronize(ctx->s_comp[0]));
+    CU(cudaStreamSynchronize(ctx->s_copy));
+    if (uniform) {
+        memcpy(out, ctx->h_dig, n * 32);
+    } else {
+        for (uint64_t k = 0; k < n; ++k) memcpy(out + 32ull * order[k], ctx->h_dig + 32ull * k, 32);
+    }
     return CAS_OK;
 }
 

@@ -7,6 +7,8 @@
 //   2  FMA pipe only  : IMAD per chain                          ( 8 instr/step)
 //   3  IMAD.HI only   : mul.hi-add per chain                    ( 8 instr/step)
 //   4  ALU + 2 IMAD   : SHF + LOP3 + IADD3 + 2 IMAD per chain   (40 instr/step)
+//   5  IMAD.WIDE only : 32x32+64 -> 64 per chain                ( 8 instr/step)
+//   6  ALU + IMAD 1:1 : SHF + LOP3 + 2 IMAD per chain           (32 instr/step)
 // The instruction mix per step is verified against the SASS in
 // tests/test_sass.py; `ops_per_thread_step` below must match it.
 #pragma once
@@ -19,7 +21,7 @@ constexpr int PEAK_THREADS = 256;
 constexpr int PEAK_UNROLL = 8;
 
 __host__ __device__ constexpr int peak_ops_per_step(int mode) {
-    return mode == 0 ? 24 : mode == 1 ? 32 : mode == 4 ? 40 : 8;
+    return mode == 0 ? 24 : (mode == 1 || mode == 6) ? 32 : mode == 4 ? 40 : 8;
 }
 
 template <int MODE>
@@ -54,6 +56,27 @@ __global__ void __launch_bounds__(PEAK_THREADS) kernel_peak(uint32_t* sink, int 
 #pragma unroll
                 for (int c = 0; c < PEAK_CHAINS; ++c)
                     asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(x[c]) : "r"(one), "r"(y[c]));
+            }
+            if (MODE == 5) {
+#pragma unroll
+                for (int c = 0; c < PEAK_CHAINS; c += 2)
+                    asm volatile("{.reg .u64 t; mov.b64 t, {%0, %1}; mad.wide.u32 t, %0, %2, t; mov.b64 {%0, %1}, t;"
+                                 " mov.b64 t, {%3, %4}; mad.wide.u32 t, %3, %2, t; mov.b64 {%3, %4}, t;}"
+                                 : "+r"(x[c]), "+r"(y[c]), "+r"(seed), "+r"(x[c + 1]), "+r"(y[c + 1]));
+            }
+            if (MODE == 6) {
+#pragma unroll
+                for (int c = 0; c < PEAK_CHAINS; ++c)
+                    asm volatile("shf.r.wrap.b32 %0, %0, %0, 7;" : "+r"(x[c]));
+#pragma unroll
+                for (int c = 0; c < PEAK_CHAINS; ++c)
+                    asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(y[c]) : "r"(one), "r"(x[c]));
+#pragma unroll
+                for (int c = 0; c < PEAK_CHAINS; ++c)
+                    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x[c]) : "r"(y[c]), "r"(one));
+#pragma unroll
+                for (int c = 0; c < PEAK_CHAINS; ++c)
+                    asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(y[c]) : "r"(one), "r"(x[c]));
             }
             if (MODE == 3) {
 #pragma unroll

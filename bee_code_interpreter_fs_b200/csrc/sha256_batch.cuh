@@ -364,17 +364,18 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS)
     const uint32_t rem = (uint32_t)(L & 63u);
     const uint32_t ntail = rem + 9u <= 64u ? 1u : 2u;
     const uint32_t nb = nfull + ntail;
-    const uint32_t nfetch = nfull + 1u;  // blocks that carry (possibly zero) message bytes
     const uint32_t bits_hi = (uint32_t)(L >> 29), bits_lo = (uint32_t)(L << 3);
     const uint32_t pad_word = rem >> 2, pad_mask = 0x80000000u >> (8u * (rem & 3u));
 
     uint32_t st[8];
     sha256_init(st);
 
+    // Every block index, tail blocks included, is fetched as a tile: past the end of
+    // the message the TMA unit delivers zeros, so the loop body has one shape.
     if (lane == 0) {
 #pragma unroll
         for (int s = 0; s < NSTAGE; ++s)
-            if ((uint32_t)s < nfetch) {
+            if ((uint32_t)s < nb) {
                 mbar_arrive_tx(bars + 8 * s, TMA_STAGE_BYTES);
                 tma_tile_2d(tiles + s * TMA_STAGE_BYTES, &tmap, (int32_t)(s * 64), (int32_t)first, bars + 8 * s);
             }
@@ -384,39 +385,32 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS)
 #pragma unroll 1
     for (uint32_t i = 0; i < nb; ++i) {
         uint32_t w[16];
-        if (i < nfetch) {
-            const uint32_t tile = tiles + stage * TMA_STAGE_BYTES + row;
-            mbar_wait(bars + 8 * stage, parity);
-            const uint4 q0 = lds_v4(tile), q1 = lds_v4(tile ^ 16u), q2 = lds_v4(tile ^ 32u), q3 = lds_v4(tile ^ 48u);
-            w[0] = bswap32(q0.x); w[1] = bswap32(q0.y); w[2] = bswap32(q0.z); w[3] = bswap32(q0.w);
-            w[4] = bswap32(q1.x); w[5] = bswap32(q1.y); w[6] = bswap32(q1.z); w[7] = bswap32(q1.w);
-            w[8] = bswap32(q2.x); w[9] = bswap32(q2.y); w[10] = bswap32(q2.z); w[11] = bswap32(q2.w);
-            w[12] = bswap32(q3.x); w[13] = bswap32(q3.y); w[14] = bswap32(q3.z); w[15] = bswap32(q3.w);
-            if (i == nfull) {  // partial block: zero-filled past the message end by the TMA unit
+        const uint32_t tile = tiles + stage * TMA_STAGE_BYTES + row;
+        mbar_wait(bars + 8 * stage, parity);
+        const uint4 q0 = lds_v4(tile), q1 = lds_v4(tile ^ 16u), q2 = lds_v4(tile ^ 32u), q3 = lds_v4(tile ^ 48u);
+        w[0] = bswap32(q0.x); w[1] = bswap32(q0.y); w[2] = bswap32(q0.z); w[3] = bswap32(q0.w);
+        w[4] = bswap32(q1.x); w[5] = bswap32(q1.y); w[6] = bswap32(q1.z); w[7] = bswap32(q1.w);
+        w[8] = bswap32(q2.x); w[9] = bswap32(q2.y); w[10] = bswap32(q2.z); w[11] = bswap32(q2.w);
+        w[12] = bswap32(q3.x); w[13] = bswap32(q3.y); w[14] = bswap32(q3.z); w[15] = bswap32(q3.w);
+        if (i >= nfull) {  // tail blocks (kernel-uniform branch, once or twice per message)
+            if (i == nfull) {
 #pragma unroll
                 for (int j = 0; j < 16; ++j) w[j] |= ((uint32_t)j == pad_word) ? pad_mask : 0u;
-                if (ntail == 1u) { w[14] = bits_hi; w[15] = bits_lo; }
             }
-        } else {  // second tail block: zeros and the bit length
-#pragma unroll
-            for (int j = 0; j < 14; ++j) w[j] = 0u;
-            w[14] = bits_hi; w[15] = bits_lo;
+            if (i + 1u == nb) { w[14] = bits_hi; w[15] = bits_lo; }
         }
         sha256_compress<FMA_LEVEL>(st, w, one);
-        if (i < nfetch) {
-            // Refill this stage.  The warp runs this loop converged, so when lane 0
-            // holds its compression result every lane's shared-memory reads of the
-            // tile have returned; the opaque dependency on st[0] keeps the issue
-            // of the copy behind them.
-            if (lane == 0 && i + NSTAGE < nfetch) {
-                uint32_t bytes;
-                asm volatile("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(bytes) : "r"(st[0]), "r"(A.zero), "r"(TMA_STAGE_BYTES));
-                mbar_arrive_tx(bars + 8 * stage, bytes);
-                tma_tile_2d(tiles + stage * TMA_STAGE_BYTES, &tmap, (int32_t)((i + NSTAGE) * 64u), (int32_t)first,
-                            bars + 8 * stage);
-            }
-            if (++stage == NSTAGE) { stage = 0; parity ^= 1u; }
+        // Refill this stage.  The warp runs this loop converged, so when lane 0 holds
+        // its compression result every lane's shared-memory reads of the tile have
+        // returned; the opaque dependency on st[0] keeps the copy behind them.
+        if (lane == 0 && i + NSTAGE < nb) {
+            uint32_t bytes;
+            asm volatile("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(bytes) : "r"(st[0]), "r"(A.zero), "r"(TMA_STAGE_BYTES));
+            mbar_arrive_tx(bars + 8 * stage, bytes);
+            tma_tile_2d(tiles + stage * TMA_STAGE_BYTES, &tmap, (int32_t)((i + NSTAGE) * 64u), (int32_t)first,
+                        bars + 8 * stage);
         }
+        if (++stage == NSTAGE) { stage = 0; parity ^= 1u; }
     }
     if (live) store_digest(A.out + t * 32u, st);
 }

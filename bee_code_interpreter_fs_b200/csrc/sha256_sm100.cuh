@@ -50,9 +50,19 @@ __device__ __forceinline__ uint32_t big_sigma0(uint32_t x) { return lop_xor3(rot
 __device__ __forceinline__ uint32_t big_sigma1(uint32_t x) { return lop_xor3(rotr32(x, 6), rotr32(x, 11), rotr32(x, 25)); }
 __device__ __forceinline__ uint32_t small_sigma0(uint32_t x) { return lop_xor3(rotr32(x, 7), rotr32(x, 18), x >> 3); }
 __device__ __forceinline__ uint32_t small_sigma1(uint32_t x) { return lop_xor3(rotr32(x, 17), rotr32(x, 19), x >> 10); }
+// x >> n as the high half of x * 2^(32-n): IMAD.HI on the FMA pipe instead of SHF on the ALU pipe.
+template <int N>
+__device__ __forceinline__ uint32_t shr_fma(uint32_t x) {
+    uint32_t d;
+    asm("mul.hi.u32 %0, %1, %2;" : "=r"(d) : "r"(x), "n"(1u << (32 - N)));
+    return d;
+}
+__device__ __forceinline__ uint32_t small_sigma0_fma(uint32_t x) { return lop_xor3(rotr32(x, 7), rotr32(x, 18), shr_fma<3>(x)); }
+__device__ __forceinline__ uint32_t small_sigma1_fma(uint32_t x) { return lop_xor3(rotr32(x, 17), rotr32(x, 19), shr_fma<10>(x)); }
 
 // FMA_LEVEL: 0 = every add where ptxas puts it; 1 = the 2-input adds on the FMA
-// pipe; 2 = additionally h+W+K as two FMA-pipe adds; 3 = every add on the FMA pipe.
+// pipe; 2 = additionally h+W+K as two FMA-pipe adds; 3 = every add on the FMA pipe;
+// 4 = level 3 plus the schedule's plain right shifts as IMAD.HI.
 template <int FMA_LEVEL>
 __device__ __forceinline__ void sha_round(uint32_t a, uint32_t b, uint32_t c, uint32_t& d, uint32_t e,
                                           uint32_t f, uint32_t g, uint32_t& h, uint32_t k, uint32_t w,
@@ -84,8 +94,8 @@ __device__ __forceinline__ void sha_round(uint32_t a, uint32_t b, uint32_t c, ui
 
 template <int FMA_LEVEL>
 __device__ __forceinline__ uint32_t sha_sched(uint32_t w16, uint32_t w15, uint32_t w7, uint32_t w2, uint32_t one) {
-    const uint32_t s0 = small_sigma0(w15);
-    const uint32_t s1 = small_sigma1(w2);
+    const uint32_t s0 = FMA_LEVEL >= 4 ? small_sigma0_fma(w15) : small_sigma0(w15);
+    const uint32_t s1 = FMA_LEVEL >= 4 ? small_sigma1_fma(w2) : small_sigma1(w2);
     if (FMA_LEVEL == 0) return w16 + s0 + w7 + s1;
     if (FMA_LEVEL <= 2) return fma_add(w16 + w7 + s0, s1, one);
     return fma_add(fma_add(fma_add(w16, w7, one), s0, one), s1, one);

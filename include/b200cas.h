@@ -41,11 +41,13 @@ typedef struct cas_ctx cas_ctx;
 /* Option keys for cas_set_option / cas_get_option. */
 #define CAS_OPT_KERNEL 1       /* load path: 0 = per-lane read-only loads, 1 = per-lane TMA bulk copies,
                                   2 = TMA 2-D tiles for uniform layouts (per-lane loads otherwise) */
-#define CAS_OPT_FMA_LEVEL 2    /* 0..3: how many of the adds run on the FMA pipe (sha256_sm100.cuh) */
-#define CAS_OPT_WAVE_BYTES 3   /* host path: bytes staged per wave (rounded to 1 MiB) */
+#define CAS_OPT_FMA_LEVEL 2    /* 0..4: how much of the arithmetic runs on the FMA pipe (sha256_sm100.cuh) */
+#define CAS_OPT_WAVE_BYTES 3   /* host path: bytes per host->device copy chunk (rounded to 1 MiB) */
 #define CAS_OPT_PACK_THREADS 4 /* host path: threads that pack objects into pinned staging */
 #define CAS_OPT_CTAS_PER_SM 5  /* resident 256-thread CTAs per SM the kernels are compiled for: 4, 3 or 2
                                   (register budget 64, 80 or 128 per thread); 0 = best measured per load path */
+
+#define CAS_OPT_ARENA_BYTES 6   /* host path: most device memory the staging arena may take (default 32 GiB) */
 
 /* Create / destroy the per-device context (streams, staging buffers are made
  * lazily).  Replaces nothing in the reference; it is the state a
@@ -65,8 +67,8 @@ int cas_device_info(const cas_ctx* ctx, int* sm_count, int* sm_clock_khz, uint64
  * (storage.py:36, :44-63), for the n objects base[off[i] .. off[i]+len[i]).
  * `base` may be NULL, in which case off[i] are absolute host addresses (how a
  * list of Python `bytes` is passed without copying).  Synchronous: host->device
- * copies (pinned, double-buffered, overlapped with the kernel), the kernel and
- * the device->host copy of the digests all happen inside the call.  Objects are
+ * copies (pinned staging, overlapped with the kernels), the kernels and the
+ * device->host copy of the digests all happen inside the call.  Objects are
  * borrowed for the call only.  out32n receives n*32 bytes, object-major.
  */
 int cas_hash_host(cas_ctx* ctx, const void* base, const uint64_t* off, const uint64_t* len, uint64_t n,

@@ -127,6 +127,38 @@ def test_host_path_random_lengths_property(hasher, kernel):
     assert hasher.hash_many(objs) == [hashlib.sha256(o).hexdigest() for o in objs]
 
 
+@pytest.mark.parametrize("pinned", [False, True])
+def test_host_path_many_epochs_and_objects_larger_than_a_chunk(hasher, pinned):
+    """Arena halves are reused across epochs and an object may span several copy chunks."""
+    saved = hasher.get_option(_ffi.OPT_ARENA_BYTES)
+    hasher.set_option(_ffi.OPT_ARENA_BYTES, 64 << 20)  # 32 MiB halves
+    hasher.set_option(_ffi.OPT_WAVE_BYTES, 4 << 20)
+    try:
+        rng = np.random.default_rng(11)
+        lengths = np.concatenate([[20 << 20, (9 << 20) + 7, 5 << 20], rng.integers(0, 300000, size=700)]).astype(np.uint64)
+        rng.shuffle(lengths)
+        off = np.concatenate([[0], np.cumsum(lengths)[:-1]]).astype(np.uint64)
+        total = int(lengths.sum())
+        assert total > 3 * (32 << 20)
+        data = rng.integers(0, 256, size=total, dtype=np.uint8)
+        if pinned:
+            host = torch.empty(total, dtype=torch.uint8).pin_memory()
+            host.numpy()[:] = data
+            got = hasher.digest_packed(host, off, lengths)
+        else:
+            got = hasher.digest_packed(data, off, lengths)
+        want = [hashlib.sha256(data[int(o):int(o) + int(n)].tobytes()).hexdigest() for o, n in zip(off, lengths)]
+        assert hexes(got) == want
+        # uniform batch over several epochs, straight from pinned memory
+        n, length = 3000, 65536
+        host = torch.empty(n * length, dtype=torch.uint8).pin_memory()
+        host.numpy()[:] = oracle.synth_batch(21, 0, n, length)
+        dig = hasher.digest_packed(host, np.arange(n, dtype=np.uint64) * length, np.full(n, length, dtype=np.uint64))
+        assert hexes(dig) == [hashlib.sha256(oracle.synth_object(21, i, length)).hexdigest() for i in range(n)]
+    finally:
+        hasher.set_option(_ffi.OPT_ARENA_BYTES, saved)
+
+
 def test_host_path_pinned_contiguous_and_mixed_types(hasher):
     n, length = 3000, 4096
     host = torch.empty(n * length, dtype=torch.uint8).pin_memory()

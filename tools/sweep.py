@@ -24,7 +24,7 @@ def main():
     ap.add_argument("--object-bytes", type=int, default=65536)
     ap.add_argument("--reps", type=int, default=3)
     ap.add_argument("--kernels", default="0,1,2")
-    ap.add_argument("--fmas", default="0,1,2,3")
+    ap.add_argument("--fmas", default="0,1,2,3,4")
     ap.add_argument("--ctas", default="4,3,2")
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "sweep.jsonl"))
     a = ap.parse_args()
@@ -38,7 +38,7 @@ def main():
     torch.cuda.synchronize()
     rows = []
     with open(a.out, "a") as f:
-        for mode in range(5):
+        for mode in range(7):
             ops, ms = h.int32_peak(mode, 8192)
             row = {"probe": mode, "lane_ops_per_s": ops, "ms": ms,
                    "lanes_per_clk_per_sm_at_max_clock": ops / (info["sm_count"] * info["sm_clock_khz"] * 1e3)}
