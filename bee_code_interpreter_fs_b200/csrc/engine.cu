@@ -95,7 +95,7 @@ private:
 };
 
 constexpr int NSTG = 3;   // pinned staging buffers in flight
-constexpr int NCOMP = 4;  // compute streams
+constexpr int NCOMP = 32;  // compute streams: launch groups overlap, so long serial chains do not queue behind each other
 
 struct Stage {
     uint8_t* h = nullptr;  // pinned staging
@@ -198,7 +198,7 @@ cudaError_t launch_one(cas_ctx* ctx, int kernel, const cas::BatchArgs& a, cudaSt
         cas::TensorMapBlob blob;
         static_assert(sizeof(blob) == sizeof(tm), "CUtensorMap is 128 bytes");
         memcpy(&blob, &tm, sizeof tm);
-        constexpr int smem = cas::tma_smem_bytes<NSTAGE, THREADS>();
+        constexpr int smem = cas::tma_smem_bytes<NSTAGE, THREADS, 1>();
         auto k = cas::kernel_tma<FMA, NSTAGE, THREADS, MIN_CTAS>;
         static bool done[16] = {};
         cudaError_t e = configure_smem(k, smem, done);

@@ -318,11 +318,6 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS) kernel_bulk(const BatchArgs
 // the lane only ORs in the 0x80 marker and the bit length.
 constexpr int TMA_STAGE_BYTES = 32 * 64;
 
-template <int NSTAGE, int THREADS>
-constexpr int tma_smem_bytes() {
-    return 1024 + (THREADS / 32) * NSTAGE * TMA_STAGE_BYTES + (THREADS / 32) * NSTAGE * 8;
-}
-
 __device__ __forceinline__ void tma_tile_2d(uint32_t dst, const void* tmap, int32_t c0, int32_t c1, uint32_t bar) {
     asm volatile(
         "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(dst),
@@ -334,18 +329,21 @@ struct alignas(64) TensorMapBlob {
     uint64_t opaque[16];  // a CUtensorMap (128 bytes), passed by value as __grid_constant__
 };
 
-template <int FMA_LEVEL, int NSTAGE, int THREADS, int MIN_CTAS>
-__global__ void __launch_bounds__(THREADS, MIN_CTAS)
-    kernel_tma(const __grid_constant__ TensorMapBlob tmap, const BatchArgs A) {
+template <int NSTAGE, int THREADS, int MSGS>
+constexpr int tma_smem_bytes() {
+    return 1024 + (THREADS / 32) * NSTAGE * (TMA_STAGE_BYTES * MSGS) + (THREADS / 32) * NSTAGE * 8;
+}
+
+template <int FMA_LEVEL, int NSTAGE, int THREADS, int MSGS, int SCHED, int PADV>
+__device__ __forceinline__ void tma_body(const TensorMapBlob& tmap, const BatchArgs& A) {
     extern __shared__ uint8_t smem_raw[];
     constexpr int WARPS = THREADS / 32;
+    constexpr uint32_t STAGE = TMA_STAGE_BYTES * MSGS;  // the tile is 32*MSGS rows of 64 bytes
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t smem_base = ((uint32_t)__cvta_generic_to_shared(smem_raw) + 1023u) & ~1023u;
-    const uint32_t tiles = smem_base + warp * NSTAGE * TMA_STAGE_BYTES;
-    const uint32_t bars = smem_base + WARPS * NSTAGE * TMA_STAGE_BYTES + warp * NSTAGE * 8;
-    // This lane's row inside a tile; its 16-byte piece c lives at row ^ (c << 4)
-    // under the 64-byte swizzle (address bits 4-5 are XORed with bits 7-8).
-    const uint32_t row = lane * 64u + (((lane >> 1) & 3u) << 4);
+    const uint32_t tiles = smem_base + warp * NSTAGE * STAGE;
+    const uint32_t bars = smem_base + WARPS * NSTAGE * STAGE + warp * NSTAGE * 8;
+    const uint32_t row = lane * 64u + (((lane >> 1) & 3u) << 4);  // message m of this lane: row + m*2048
 
     if (lane == 0) {
 #pragma unroll
@@ -355,9 +353,7 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS)
     }
     __syncwarp();
 
-    const uint64_t first = (uint64_t)blockIdx.x * THREADS + warp * 32u;  // first object of this warp
-    const uint64_t t = first + lane;
-    const bool live = t < A.n;
+    const uint64_t first = ((uint64_t)blockIdx.x * WARPS + warp) * (32u * MSGS);
     const uint32_t one = A.one;
     const uint64_t L = A.ulen;
     const uint32_t nfull = (uint32_t)(L >> 6);
@@ -365,54 +361,79 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS)
     const uint32_t ntail = rem + 9u <= 64u ? 1u : 2u;
     const uint32_t nb = nfull + ntail;
     const uint32_t bits_hi = (uint32_t)(L >> 29), bits_lo = (uint32_t)(L << 3);
-    const uint32_t pad_word = rem >> 2, pad_mask = 0x80000000u >> (8u * (rem & 3u));
 
-    uint32_t st[8];
-    sha256_init(st);
+    uint32_t st[MSGS][8];
+#pragma unroll
+    for (int m = 0; m < MSGS; ++m) sha256_init(st[m]);
 
-    // Every block index, tail blocks included, is fetched as a tile: past the end of
-    // the message the TMA unit delivers zeros, so the loop body has one shape.
     if (lane == 0) {
 #pragma unroll
         for (int s = 0; s < NSTAGE; ++s)
             if ((uint32_t)s < nb) {
-                mbar_arrive_tx(bars + 8 * s, TMA_STAGE_BYTES);
-                tma_tile_2d(tiles + s * TMA_STAGE_BYTES, &tmap, (int32_t)(s * 64), (int32_t)first, bars + 8 * s);
+                mbar_arrive_tx(bars + 8 * s, STAGE);
+                tma_tile_2d(tiles + s * STAGE, &tmap, (int32_t)(s * 64), (int32_t)first, bars + 8 * s);
             }
     }
 
     uint32_t stage = 0, parity = 0;
 #pragma unroll 1
     for (uint32_t i = 0; i < nb; ++i) {
-        uint32_t w[16];
-        const uint32_t tile = tiles + stage * TMA_STAGE_BYTES + row;
+        uint32_t w[MSGS][16];
+        const uint32_t tile = tiles + stage * STAGE + row;
         mbar_wait(bars + 8 * stage, parity);
-        const uint4 q0 = lds_v4(tile), q1 = lds_v4(tile ^ 16u), q2 = lds_v4(tile ^ 32u), q3 = lds_v4(tile ^ 48u);
-        w[0] = bswap32(q0.x); w[1] = bswap32(q0.y); w[2] = bswap32(q0.z); w[3] = bswap32(q0.w);
-        w[4] = bswap32(q1.x); w[5] = bswap32(q1.y); w[6] = bswap32(q1.z); w[7] = bswap32(q1.w);
-        w[8] = bswap32(q2.x); w[9] = bswap32(q2.y); w[10] = bswap32(q2.z); w[11] = bswap32(q2.w);
-        w[12] = bswap32(q3.x); w[13] = bswap32(q3.y); w[14] = bswap32(q3.z); w[15] = bswap32(q3.w);
+#pragma unroll
+        for (int m = 0; m < MSGS; ++m) {
+            const uint32_t t = tile + m * TMA_STAGE_BYTES;
+            const uint4 q0 = lds_v4(t), q1 = lds_v4(t ^ 16u), q2 = lds_v4(t ^ 32u), q3 = lds_v4(t ^ 48u);
+            w[m][0] = bswap32(q0.x); w[m][1] = bswap32(q0.y); w[m][2] = bswap32(q0.z); w[m][3] = bswap32(q0.w);
+            w[m][4] = bswap32(q1.x); w[m][5] = bswap32(q1.y); w[m][6] = bswap32(q1.z); w[m][7] = bswap32(q1.w);
+            w[m][8] = bswap32(q2.x); w[m][9] = bswap32(q2.y); w[m][10] = bswap32(q2.z); w[m][11] = bswap32(q2.w);
+            w[m][12] = bswap32(q3.x); w[m][13] = bswap32(q3.y); w[m][14] = bswap32(q3.z); w[m][15] = bswap32(q3.w);
+        }
         if (i >= nfull) {  // tail blocks (kernel-uniform branch, once or twice per message)
             if (i == nfull) {
+                uint32_t r = rem;
+                if (PADV == 1) asm volatile("" : "+r"(r));  // keeps the 16 masks out of loop-invariant registers
+                const uint32_t pad_word = r >> 2, pad_mask = 0x80000000u >> (8u * (r & 3u));
 #pragma unroll
-                for (int j = 0; j < 16; ++j) w[j] |= ((uint32_t)j == pad_word) ? pad_mask : 0u;
+                for (int m = 0; m < MSGS; ++m)
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) w[m][j] |= ((uint32_t)j == pad_word) ? pad_mask : 0u;
             }
-            if (i + 1u == nb) { w[14] = bits_hi; w[15] = bits_lo; }
+            if (i + 1u == nb) {
+#pragma unroll
+                for (int m = 0; m < MSGS; ++m) { w[m][14] = bits_hi; w[m][15] = bits_lo; }
+            }
         }
-        sha256_compress<FMA_LEVEL>(st, w, one);
-        // Refill this stage.  The warp runs this loop converged, so when lane 0 holds
-        // its compression result every lane's shared-memory reads of the tile have
-        // returned; the opaque dependency on st[0] keeps the copy behind them.
+        sha256_compress_multi<FMA_LEVEL, MSGS, SCHED>(st, w, one);
         if (lane == 0 && i + NSTAGE < nb) {
             uint32_t bytes;
-            asm volatile("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(bytes) : "r"(st[0]), "r"(A.zero), "r"(TMA_STAGE_BYTES));
+            asm volatile("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(bytes) : "r"(st[0][0] | st[MSGS - 1][0]), "r"(A.zero), "r"(STAGE));
             mbar_arrive_tx(bars + 8 * stage, bytes);
-            tma_tile_2d(tiles + stage * TMA_STAGE_BYTES, &tmap, (int32_t)((i + NSTAGE) * 64u), (int32_t)first,
-                        bars + 8 * stage);
+            tma_tile_2d(tiles + stage * STAGE, &tmap, (int32_t)((i + NSTAGE) * 64u), (int32_t)first, bars + 8 * stage);
         }
         if (++stage == NSTAGE) { stage = 0; parity ^= 1u; }
     }
-    if (live) store_digest(A.out + t * 32u, st);
+#pragma unroll
+    for (int m = 0; m < MSGS; ++m) {
+        const uint64_t t = first + lane + 32u * m;
+        if (t < A.n) store_digest(A.out + t * 32u, st[m]);
+    }
+}
+
+
+// Register budget either from __launch_bounds__(THREADS, MIN_CTAS) or, finer, from
+// __maxnreg__(REGCAP).  ptxas' instruction schedule (and with it 5-8 % of the
+// throughput) changes with the budget; tools/kbench_build.py sweeps both.
+template <int FMA_LEVEL, int NSTAGE, int THREADS, int MIN_CTAS, int MSGS = 1, int SCHED = 0, int PADV = 1>
+__global__ void __launch_bounds__(THREADS, MIN_CTAS)
+    kernel_tma(const __grid_constant__ TensorMapBlob tmap, const BatchArgs A) {
+    tma_body<FMA_LEVEL, NSTAGE, THREADS, MSGS, SCHED, PADV>(tmap, A);
+}
+template <int FMA_LEVEL, int NSTAGE, int THREADS, int REGCAP, int MSGS = 1, int SCHED = 0, int PADV = 1>
+__global__ void __launch_bounds__(THREADS) __maxnreg__(REGCAP)
+    kernel_tma_regcap(const __grid_constant__ TensorMapBlob tmap, const BatchArgs A) {
+    tma_body<FMA_LEVEL, NSTAGE, THREADS, MSGS, SCHED, PADV>(tmap, A);
 }
 
 }  // namespace cas

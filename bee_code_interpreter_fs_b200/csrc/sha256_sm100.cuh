@@ -145,6 +145,58 @@ __device__ __forceinline__ void sha256_compress(uint32_t (&st)[8], uint32_t (&w)
     }
 }
 
+__host__ __device__ constexpr uint32_t k256(int i) {
+    constexpr uint32_t K[64] = {
+        0x428a2f98u, 0x71374491u, 0xb5c0fbcfu, 0xe9b5dba5u, 0x3956c25bu, 0x59f111f1u, 0x923f82a4u, 0xab1c5ed5u,
+        0xd807aa98u, 0x12835b01u, 0x243185beu, 0x550c7dc3u, 0x72be5d74u, 0x80deb1feu, 0x9bdc06a7u, 0xc19bf174u,
+        0xe49b69c1u, 0xefbe4786u, 0x0fc19dc6u, 0x240ca1ccu, 0x2de92c6fu, 0x4a7484aau, 0x5cb0a9dcu, 0x76f988dau,
+        0x983e5152u, 0xa831c66du, 0xb00327c8u, 0xbf597fc7u, 0xc6e00bf3u, 0xd5a79147u, 0x06ca6351u, 0x14292967u,
+        0x27b70a85u, 0x2e1b2138u, 0x4d2c6dfcu, 0x53380d13u, 0x650a7354u, 0x766a0abbu, 0x81c2c92eu, 0x92722c85u,
+        0xa2bfe8a1u, 0xa81a664bu, 0xc24b8b70u, 0xc76c51a3u, 0xd192e819u, 0xd6990624u, 0xf40e3585u, 0x106aa070u,
+        0x19a4c116u, 0x1e376c08u, 0x2748774cu, 0x34b0bcb5u, 0x391c0cb3u, 0x4ed8aa4au, 0x5b9cca4fu, 0x682e6ff3u,
+        0x748f82eeu, 0x78a5636fu, 0x84c87814u, 0x8cc70208u, 0x90befffau, 0xa4506cebu, 0xbef9a3f7u, 0xc67178f2u};
+    return K[i];
+}
+
+// M interleaved compressions: round i of every message before round i+1 of any
+// (M = 2 measured slower than M = 1 with twice the warps on B200; kept for the record).
+// SCHED 0: schedule words 8 at a time ahead of 8 rounds; 1: one word right before its round.
+template <int FMA_LEVEL, int M, int SCHED>
+__device__ __forceinline__ void sha256_compress_multi(uint32_t (&st)[M][8], uint32_t (&w)[M][16], uint32_t one) {
+    uint32_t v[M][8];
+#pragma unroll
+    for (int m = 0; m < M; ++m)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[m][j] = st[m][j];
+#pragma unroll
+    for (int i = 0; i < 64; ++i) {
+        if (SCHED == 0) {
+            if (i >= 16 && (i & 7) == 0) {
+#pragma unroll
+                for (int j = i; j < i + 8; ++j)
+#pragma unroll
+                    for (int m = 0; m < M; ++m)
+                        w[m][j & 15] = sha_sched<FMA_LEVEL>(w[m][j & 15], w[m][(j + 1) & 15], w[m][(j + 9) & 15],
+                                                            w[m][(j + 14) & 15], one);
+            }
+        } else if (i >= 16) {
+#pragma unroll
+            for (int m = 0; m < M; ++m)
+                w[m][i & 15] = sha_sched<FMA_LEVEL>(w[m][i & 15], w[m][(i + 1) & 15], w[m][(i + 9) & 15],
+                                                    w[m][(i + 14) & 15], one);
+        }
+#pragma unroll
+        for (int m = 0; m < M; ++m)
+            sha_round<FMA_LEVEL>(v[m][(64 - i) & 7], v[m][(65 - i) & 7], v[m][(66 - i) & 7], v[m][(67 - i) & 7],
+                                 v[m][(68 - i) & 7], v[m][(69 - i) & 7], v[m][(70 - i) & 7], v[m][(71 - i) & 7],
+                                 k256(i), w[m][i & 15], one);
+    }
+#pragma unroll
+    for (int m = 0; m < M; ++m)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) st[m][j] = FMA_LEVEL == 0 ? st[m][j] + v[m][j] : fma_add(st[m][j], v[m][j], one);
+}
+
 __device__ __forceinline__ void sha256_init(uint32_t (&st)[8]) {
     st[0] = 0x6a09e667u; st[1] = 0xbb67ae85u; st[2] = 0x3c6ef372u; st[3] = 0xa54ff53au;
     st[4] = 0x510e527fu; st[5] = 0x9b05688cu; st[6] = 0x1f83d9abu; st[7] = 0x5be0cd19u;
