@@ -31,6 +31,7 @@
 #include "../../include/b200cas.h"
 #include "peak.cuh"
 #include "sha256_batch.cuh"
+#include "sha256_long.cuh"
 #include "synth.cuh"
 
 namespace {
@@ -120,6 +121,8 @@ struct cas_ctx {
     int pack_threads = 0;
     uint64_t launches = 0;
     uint64_t arena_max = 32ull << 30;  // device bytes the host path may hold (two halves)
+    uint64_t long_max_objects = 1536;  // batches up to this many objects may go one warp per object
+    uint64_t long_min_bytes = 32768;   // ... if the objects are at least this long
     cudaStream_t s_copy = nullptr;
     cudaStream_t s_comp[NCOMP] = {};
     cudaEvent_t ev_epoch[2][NCOMP] = {};  // kernels of the epoch that last used an arena half
@@ -242,6 +245,19 @@ int launch_batch(cas_ctx* ctx, cas::BatchArgs a, cudaStream_t st) {
         default: e = launch_occ<4>(ctx, ctx->kernel, a, st); break;
     }
     if (e != cudaSuccess) return fail(ctx, CAS_E_CUDA, "sha256 batch kernel launch", e);
+    ++ctx->launches;
+    return CAS_OK;
+}
+
+// One warp per object (csrc/sha256_long.cuh): for few, long objects.
+int launch_long(cas_ctx* ctx, cas::BatchArgs a, cudaStream_t st) {
+    if (a.n == 0) return CAS_OK;
+    if (a.n > 0x7FFFFFFFull) return fail(ctx, CAS_E_ARG, "too many objects for the warp-per-object kernel");
+    a.one = 1u;
+    a.zero = 0u;
+    cas::kernel_long<3, 1><<<(unsigned)a.n, 32, cas::LONG_SMEM_PER_WARP, st>>>(a);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(ctx, CAS_E_CUDA, "sha256 warp-per-object kernel launch", e);
     ++ctx->launches;
     return CAS_OK;
 }
@@ -432,6 +448,14 @@ int cas_set_option(cas_ctx* ctx, int key, int64_t v) {
             if (v < (int64_t)(64 * MiB)) return fail(ctx, CAS_E_ARG, "CAS_OPT_ARENA_BYTES must be >= 64 MiB");
             ctx->arena_max = (uint64_t)v;
             return CAS_OK;
+        case CAS_OPT_LONG_MAX_OBJECTS:
+            if (v < 0 || v > (1 << 20)) return fail(ctx, CAS_E_ARG, "CAS_OPT_LONG_MAX_OBJECTS must be 0..2^20");
+            ctx->long_max_objects = (uint64_t)v;
+            return CAS_OK;
+        case CAS_OPT_LONG_MIN_BYTES:
+            if (v < 64) return fail(ctx, CAS_E_ARG, "CAS_OPT_LONG_MIN_BYTES must be >= 64");
+            ctx->long_min_bytes = (uint64_t)v;
+            return CAS_OK;
         case CAS_OPT_CTAS_PER_SM:
             if (v != 0 && (v < 2 || v > 4)) return fail(ctx, CAS_E_ARG, "CAS_OPT_CTAS_PER_SM must be 0 (auto), 2, 3 or 4");
             ctx->ctas_per_sm = (int)v;
@@ -449,6 +473,8 @@ int cas_get_option(const cas_ctx* ctx, int key, int64_t* v) {
         case CAS_OPT_PACK_THREADS: *v = ctx->pool ? ctx->pool->size() : ctx->pack_threads; return CAS_OK;
         case CAS_OPT_CTAS_PER_SM: *v = ctx->ctas_per_sm; return CAS_OK;
         case CAS_OPT_ARENA_BYTES: *v = (int64_t)ctx->arena_max; return CAS_OK;
+        case CAS_OPT_LONG_MAX_OBJECTS: *v = (int64_t)ctx->long_max_objects; return CAS_OK;
+        case CAS_OPT_LONG_MIN_BYTES: *v = (int64_t)ctx->long_min_bytes; return CAS_OK;
     }
     return CAS_E_ARG;
 }
@@ -479,6 +505,22 @@ int cas_hash_device(cas_ctx* ctx, const void* d_base, const uint64_t* d_off, con
     return launch_batch(ctx, a, static_cast<cudaStream_t>(stream));
 }
 
+int cas_hash_device_long(cas_ctx* ctx, const void* d_base, const uint64_t* d_off, const uint64_t* d_len,
+                         const uint32_t* d_order, uint64_t n, void* d_out, void* stream) {
+    if (!ctx) return CAS_E_ARG;
+    if (n == 0) return CAS_OK;
+    if (!d_off || !d_len || !d_out) return fail(ctx, CAS_E_ARG, "cas_hash_device_long: NULL offset/length/output array");
+    CU(cudaSetDevice(ctx->device));
+    cas::BatchArgs a{};
+    a.base = static_cast<const uint8_t*>(d_base);
+    a.off = d_off;
+    a.len = d_len;
+    a.order = d_order;
+    a.n = n;
+    a.out = static_cast<uint8_t*>(d_out);
+    return launch_long(ctx, a, static_cast<cudaStream_t>(stream));
+}
+
 int cas_hash_device_uniform(cas_ctx* ctx, const void* d_base, uint64_t stride, uint64_t len, uint64_t n,
                             void* d_out, void* stream) {
     if (!ctx) return CAS_E_ARG;
@@ -492,6 +534,9 @@ int cas_hash_device_uniform(cas_ctx* ctx, const void* d_base, uint64_t stride, u
     a.ulen = len;
     a.n = n;
     a.out = static_cast<uint8_t*>(d_out);
+    // Few long objects: lane-per-object would leave the GPU empty and every chain slow.
+    if (n <= ctx->long_max_objects && len >= ctx->long_min_bytes)
+        return launch_long(ctx, a, static_cast<cudaStream_t>(stream));
     return launch_batch(ctx, a, static_cast<cudaStream_t>(stream));
 }
 
@@ -577,6 +622,17 @@ int cas_hash_host(cas_ctx* ctx, const void* base, const uint64_t* off, const uin
     if (!uniform)
         std::stable_sort(order.begin(), order.end(),
                          [&](uint32_t a, uint32_t b) { return nblocks(len[a]) > nblocks(len[b]); });
+
+    // The longest objects go one warp per object when their serial chains, not the
+    // batch's total work, would set the time (a few big files among many small ones).
+    uint64_t n_long = 0;
+    if (!uniform || n <= ctx->long_max_objects) {
+        const double t_serial = (double)maxlen / 25e6, t_bulk = (double)total / 900e9;
+        if (t_serial > 2.0 * t_bulk) {
+            const uint64_t floor_len = std::max<uint64_t>(ctx->long_min_bytes, maxlen / 4);
+            while (n_long < n && n_long < ctx->long_max_objects && len[order[n_long]] >= floor_len) ++n_long;
+        }
+    }
 
     // Chunk (copy granule) and arena sizes.  Small batches are cut finer so that copy
     // and hash still overlap; the arena has two halves so that the copies of one epoch
@@ -671,18 +727,21 @@ int cas_hash_host(cas_ctx* ctx, const void* base, const uint64_t* off, const uin
             uint64_t kend = klaunch;
             while (kend < k1 && h_off[kend] + h_len[kend] <= c1) ++kend;
             if (c1 >= bytes) kend = k1;
-            if (kend > klaunch) {
+            while (kend > klaunch) {
+                // [klaunch, split) goes one warp per object, [split, kend) one lane per object.
+                const bool is_long = klaunch < n_long;
+                const uint64_t split = is_long ? std::min(kend, n_long) : kend;
                 cudaStream_t cs = ctx->s_comp[launch_no % NCOMP];
                 CU(cudaStreamWaitEvent(cs, sg.ev, 0));
                 cas::BatchArgs a{};
                 a.base = d_base;
                 a.off = ctx->d_meta + klaunch;
                 a.len = ctx->d_meta + n + klaunch;
-                a.n = kend - klaunch;
+                a.n = split - klaunch;
                 a.out = ctx->d_dig + 32ull * klaunch;
-                if ((rc = launch_batch(ctx, a, cs))) return rc;
+                if ((rc = is_long ? launch_long(ctx, a, cs) : launch_batch(ctx, a, cs))) return rc;
                 ++launch_no;
-                klaunch = kend;
+                klaunch = split;
             }
             if (c1 >= bytes) break;
         }

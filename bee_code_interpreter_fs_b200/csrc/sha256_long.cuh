@@ -1,0 +1,153 @@
+// Long messages, few of them: one WARP per message.
+//
+// With lane-per-message a batch of a few large objects (BASELINE config 5, the big
+// files of config 4, a single upload) leaves the GPU almost empty and every chain
+// runs at the speed of one lane.  SHA-256 cannot be split inside a message, but the
+// message schedule can: W[16..63] of a block depends only on that block's bytes.
+// So the warp alternates between
+//   phase A  lane l expands the schedule of block (32 g + l) and stores W[t] + K[t]
+//            (64 words) to shared memory: 32 blocks in parallel, coalesced loads;
+//   phase B  the 64 rounds of those 32 blocks, one block after the other, every lane
+//            running the same chain from broadcast LDS.128 reads: 10 logic
+//            instructions per round are left on the serial path instead of ~27.
+// The serial path is then bounded by the ALU-pipe occupancy of a single warp and the
+// round's dependency chain (about 1.3-1.5 k cycles per block), ~3x the lane-per-message
+// rate; the digest is unchanged.
+#pragma once
+#include "sha256_batch.cuh"
+
+namespace cas {
+
+constexpr int LONG_GROUP = 32;             // blocks expanded per phase A (one per lane)
+constexpr int LONG_PITCH = 64 * 4 + 16;    // bytes per expanded block; +16 keeps STS.128 conflict-free
+constexpr int LONG_SMEM_PER_WARP = LONG_GROUP * LONG_PITCH;
+
+__device__ __forceinline__ void sts_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+
+// One round given wk = W[t] + K[t].  ADDS 0: plain adds (ptxas picks IADD3 / IMAD.IADD);
+// 1: shortest dependency chain -- both new values are one 3-input add after Sigma;
+// 2: every add a 2-input add on the FMA pipe.
+template <int ADDS>
+__device__ __forceinline__ void long_round(uint32_t a, uint32_t b, uint32_t c, uint32_t& d, uint32_t e, uint32_t f,
+                                           uint32_t g, uint32_t& h, uint32_t wk, uint32_t one) {
+    const uint32_t s1 = big_sigma1(e);
+    const uint32_t ch = lop_ch(e, f, g);
+    const uint32_t s0 = big_sigma0(a);
+    const uint32_t mj = lop_maj(a, b, c);
+    if (ADDS == 0) {
+        const uint32_t t1 = h + wk + s1 + ch;
+        d += t1;
+        h = t1 + s0 + mj;
+    } else if (ADDS == 1) {
+        const uint32_t x = fma_add(h, wk, one);   // off the critical path: h and d are three rounds old
+        const uint32_t x2 = fma_add(x, d, one);
+        const uint32_t p = x + ch + mj;
+        d = x2 + ch + s1;
+        h = p + s1 + s0;
+    } else {
+        const uint32_t x = fma_add(h, wk, one);
+        const uint32_t t1 = fma_add(fma_add(x, ch, one), s1, one);
+        d = fma_add(d, t1, one);
+        h = fma_add(fma_add(t1, mj, one), s0, one);
+    }
+}
+
+template <int FMA_LEVEL, int ADDS>
+__global__ void __launch_bounds__(32) kernel_long(const BatchArgs A) {
+    extern __shared__ __align__(16) uint8_t smem_long[];
+    const uint32_t lane = threadIdx.x & 31;
+    const uint64_t t = blockIdx.x;  // one warp (one CTA) per message
+    uint64_t idx, L;
+    const uint8_t* p;
+    if (!locate(A, t, idx, p, L)) return;
+    const uint32_t one = A.one;
+    const uint64_t nfull = L >> 6;
+    const uint32_t rem = (uint32_t)(L & 63u);
+    const uint32_t ntail = rem + 9u <= 64u ? 1u : 2u;
+    const uint64_t nb = nfull + ntail;
+    const bool al = ((uintptr_t)p & 15u) == 0;
+    const uint32_t rows = (uint32_t)__cvta_generic_to_shared(smem_long);
+    const uint32_t my_row = rows + lane * LONG_PITCH;
+
+    uint32_t st[8];
+    sha256_init(st);
+
+    uint4 q0, q1, q2, q3;
+    q0 = q1 = q2 = q3 = make_uint4(0, 0, 0, 0);
+    if (al && lane < nfull) {
+        const uint8_t* s = p + ((uint64_t)lane << 6);
+        q0 = ldg_nc_v4(s); q1 = ldg_nc_v4(s + 16); q2 = ldg_nc_v4(s + 32); q3 = ldg_nc_v4(s + 48);
+    }
+#pragma unroll 1
+    for (uint64_t g0 = 0; g0 < nb; g0 += LONG_GROUP) {
+        // ---- phase A: this lane expands block j ------------------------------------------
+        const uint64_t j = g0 + lane;
+        if (j < nb) {
+            uint32_t w[16];
+            if (j < nfull) {
+                if (al) {
+                    w[0] = bswap32(q0.x); w[1] = bswap32(q0.y); w[2] = bswap32(q0.z); w[3] = bswap32(q0.w);
+                    w[4] = bswap32(q1.x); w[5] = bswap32(q1.y); w[6] = bswap32(q1.z); w[7] = bswap32(q1.w);
+                    w[8] = bswap32(q2.x); w[9] = bswap32(q2.y); w[10] = bswap32(q2.z); w[11] = bswap32(q2.w);
+                    w[12] = bswap32(q3.x); w[13] = bswap32(q3.y); w[14] = bswap32(q3.z); w[15] = bswap32(q3.w);
+                } else {
+                    load_block_unaligned(p + (j << 6), w);
+                }
+            } else {
+                uint32_t tw[16];
+                build_tail_block(p + (nfull << 6), rem, L, (uint32_t)(j - nfull), ntail, tw);
+#pragma unroll
+                for (int i = 0; i < 16; ++i) w[i] = tw[i];
+            }
+#pragma unroll
+            for (int i = 0; i < 64; i += 4) {
+                uint32_t o[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int r = i + u;
+                    if (r >= 16)
+                        w[r & 15] = sha_sched<FMA_LEVEL>(w[r & 15], w[(r + 1) & 15], w[(r + 9) & 15], w[(r + 14) & 15], one);
+                    o[u] = w[r & 15] + k256(r);
+                }
+                sts_v4(my_row + i * 4, o[0], o[1], o[2], o[3]);
+            }
+        }
+        // The next group's bytes travel while this group's rounds run.
+        {
+            const uint64_t jn = j + LONG_GROUP;
+            if (al && jn < nfull) {
+                const uint8_t* s = p + (jn << 6);
+                q0 = ldg_nc_v4(s); q1 = ldg_nc_v4(s + 16); q2 = ldg_nc_v4(s + 32); q3 = ldg_nc_v4(s + 48);
+            }
+        }
+        __syncwarp();
+        // ---- phase B: the serial chain over the expanded blocks ---------------------------
+        const uint32_t cnt = (uint32_t)(nb - g0 < LONG_GROUP ? nb - g0 : LONG_GROUP);
+#pragma unroll 1
+        for (uint32_t b = 0; b < cnt; ++b) {
+            const uint32_t row = rows + b * LONG_PITCH;
+            uint32_t v[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v[i] = st[i];
+#pragma unroll
+            for (int i = 0; i < 64; i += 4) {
+                const uint4 k4 = lds_v4(row + i * 4);
+                const uint32_t wk[4] = {k4.x, k4.y, k4.z, k4.w};
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int r = i + u;
+                    long_round<ADDS>(v[(64 - r) & 7], v[(65 - r) & 7], v[(66 - r) & 7], v[(67 - r) & 7], v[(68 - r) & 7],
+                                     v[(69 - r) & 7], v[(70 - r) & 7], v[(71 - r) & 7], wk[u], one);
+                }
+            }
+#pragma unroll
+            for (int i = 0; i < 8; ++i) st[i] += v[i];
+        }
+        __syncwarp();
+    }
+    if (lane == 0) store_digest(A.out + idx * 32u, st);
+}
+
+}  // namespace cas

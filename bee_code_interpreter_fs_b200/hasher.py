@@ -139,10 +139,11 @@ class GpuHasher:
         return self.hash_many([data])[0]
 
     # -- device buffers (kernel-only path) ------------------------------------
-    def digest_device(self, base, off, length, order=None, out=None, stream=None):
+    def digest_device(self, base, off, length, order=None, out=None, stream=None, warp_per_object=False):
         """Hash objects resident in device memory. ``base`` is a CUDA uint8 tensor (or
         pointer), ``off``/``length`` CUDA int64/uint64 tensors; returns a CUDA (n, 32)
-        uint8 tensor. Asynchronous on ``stream`` (a torch stream) or the current stream."""
+        uint8 tensor. Asynchronous on ``stream`` (a torch stream) or the current stream.
+        ``warp_per_object`` selects the kernel for few, long objects (cas_hash_device_long)."""
         import torch
 
         n = int(off.numel())
@@ -153,9 +154,10 @@ class GpuHasher:
             stream = torch.cuda.current_stream(dev)
         bptr = base.data_ptr() if hasattr(base, "data_ptr") else int(base)
         optr = order.data_ptr() if order is not None else 0
+        fn = self._lib.cas_hash_device_long if warp_per_object else self._lib.cas_hash_device
         with self._lock:
-            self._check(self._lib.cas_hash_device(self._ctx, bptr, off.data_ptr(), length.data_ptr(), optr, n,
-                                                  out.data_ptr(), self._stream_handle(stream)))
+            self._check(fn(self._ctx, bptr, off.data_ptr(), length.data_ptr(), optr, n, out.data_ptr(),
+                           self._stream_handle(stream)))
         return out
 
     def digest_device_uniform(self, base, stride: int, length: int, n: int, out=None, stream=None):

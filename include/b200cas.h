@@ -49,6 +49,9 @@ typedef struct cas_ctx cas_ctx;
 
 #define CAS_OPT_ARENA_BYTES 6   /* host path: most device memory the staging arena may take (default 32 GiB) */
 
+#define CAS_OPT_LONG_MAX_OBJECTS 7 /* batches of at most this many objects may run one warp per object (default 1536; 0 = never) */
+#define CAS_OPT_LONG_MIN_BYTES 8   /* ... when the objects are at least this long (default 32 KiB) */
+
 /* Create / destroy the per-device context (streams, staging buffers are made
  * lazily).  Replaces nothing in the reference; it is the state a
  * `Storage(storage_path)` instance would own (storage.py:41-42). */
@@ -85,8 +88,19 @@ int cas_hash_host(cas_ctx* ctx, const void* base, const uint64_t* off, const uin
 int cas_hash_device(cas_ctx* ctx, const void* d_base, const uint64_t* d_off, const uint64_t* d_len,
                     const uint32_t* d_order, uint64_t n, void* d_out, void* stream);
 
+/*
+ * Same contract as cas_hash_device, but one WARP per object instead of one lane: the
+ * message schedule of 32 blocks is expanded in parallel by the warp's lanes and only the
+ * 64 rounds stay on the serial chain.  About 3x faster per object; use it when the batch
+ * has so few objects (up to ~1.5 k) that lanes would leave the GPU empty -- BASELINE.json
+ * config 5 (64 x 1 GiB), a single large upload.  Digests are identical.
+ */
+int cas_hash_device_long(cas_ctx* ctx, const void* d_base, const uint64_t* d_off, const uint64_t* d_len,
+                         const uint32_t* d_order, uint64_t n, void* d_out, void* stream);
+
 /* Uniform layout: object i is d_base[i*stride .. i*stride+len). The shape of
- * BASELINE.json configs 2 and 3 (1M x 4 KiB / 64 KiB). */
+ * BASELINE.json configs 2, 3 and 5 (1M x 4 KiB / 64 KiB, 64 x 1 GiB).  Small batches of
+ * long objects (CAS_OPT_LONG_*) run one warp per object. */
 int cas_hash_device_uniform(cas_ctx* ctx, const void* d_base, uint64_t stride, uint64_t len, uint64_t n,
                             void* d_out, void* stream);
 

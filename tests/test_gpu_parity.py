@@ -16,7 +16,7 @@ from oracle import sha256_oracle as oracle
 pytestmark = pytest.mark.gpu
 
 KERNELS = [0, 1, 2]
-FMA_LEVELS = [0, 1, 2, 3]
+FMA_LEVELS = [0, 1, 2, 3, 4]
 
 
 def configure(h, kernel=None, fma=None, ctas=None):
@@ -31,7 +31,7 @@ def configure(h, kernel=None, fma=None, ctas=None):
 @pytest.fixture(autouse=True)
 def restore_defaults(hasher):
     saved = {k: hasher.get_option(k) for k in (_ffi.OPT_KERNEL, _ffi.OPT_FMA_LEVEL, _ffi.OPT_CTAS_PER_SM,
-                                              _ffi.OPT_WAVE_BYTES)}
+                                              _ffi.OPT_WAVE_BYTES, _ffi.OPT_LONG_MAX_OBJECTS, _ffi.OPT_LONG_MIN_BYTES)}
     yield
     for k, v in saved.items():
         hasher.set_option(k, v)
@@ -114,6 +114,44 @@ def test_ragged_device_path_any_alignment(hasher, kernel, align):
     order = torch.from_numpy(np.argsort(-lengths, kind="stable").astype(np.uint32).view(np.int32)).cuda()
     got2 = hexes(hasher.digest_device(d_blob, d_off, d_len, order=order).cpu().numpy())
     assert got2 == want
+
+
+@pytest.mark.parametrize("align", [16, 1])
+def test_warp_per_object_kernel_any_length_any_alignment(hasher, align):
+    """cas_hash_device_long: schedule expanded by 32 lanes, rounds serial; same digests."""
+    rng = np.random.default_rng(99 + align)
+    lengths = np.array([0, 1, 55, 56, 63, 64, 65, 119, 120, 127, 128, 2047, 2048, 2049, 2111, 2112, 4095, 4096,
+                        65536, 100001, (1 << 20) + 3] + rng.integers(0, 9000, size=40).tolist())
+    slots = (lengths + align - 1) // align * align + (0 if align > 1 else rng.integers(0, 3, size=lengths.size))
+    off = np.concatenate([[0], np.cumsum(slots)[:-1]]).astype(np.uint64)
+    if align == 1:
+        off += 3
+    blob = rng.integers(0, 256, size=int(off[-1] + lengths[-1] + 64), dtype=np.uint8)
+    d_blob = torch.from_numpy(blob).cuda()
+    d_off = torch.from_numpy(off.astype(np.int64)).cuda()
+    d_len = torch.from_numpy(lengths.astype(np.int64)).cuda()
+    want = [hashlib.sha256(blob[int(o):int(o) + int(n)].tobytes()).hexdigest() for o, n in zip(off, lengths)]
+    got = hexes(hasher.digest_device(d_blob, d_off, d_len, warp_per_object=True).cpu().numpy())
+    assert got == want
+    order = torch.from_numpy(np.argsort(-lengths, kind="stable").astype(np.int32)).cuda()
+    got = hexes(hasher.digest_device(d_blob, d_off, d_len, order=order, warp_per_object=True).cpu().numpy())
+    assert got == want
+
+
+def test_few_long_uniform_objects_take_the_warp_kernel_and_agree_with_lanes(hasher):
+    n, length = 40, (3 << 20) + 17
+    stride = (length + 15) // 16 * 16
+    buf = torch.empty(n * stride, dtype=torch.uint8, device="cuda:0")
+    hasher.gen_synthetic(buf, 123, 0, n, length, stride)
+    a = hexes(hasher.digest_device_uniform(buf, stride, length, n).cpu().numpy())  # warp per object (n small)
+    hasher.set_option(_ffi.OPT_LONG_MAX_OBJECTS, 0)
+    try:
+        b = hexes(hasher.digest_device_uniform(buf, stride, length, n).cpu().numpy())  # lane per object
+    finally:
+        hasher.set_option(_ffi.OPT_LONG_MAX_OBJECTS, 1536)
+    assert a == b
+    assert a[0] == hashlib.sha256(oracle.synth_object(123, 0, length)).hexdigest()
+    assert a[-1] == hashlib.sha256(oracle.synth_object(123, n - 1, length)).hexdigest()
 
 
 # ------------------------------------------------------------ host path (e2e) --
