@@ -96,7 +96,7 @@ private:
 };
 
 constexpr int NSTG = 3;   // pinned staging buffers in flight
-constexpr int NCOMP = 32;  // compute streams: launch groups overlap, so long serial chains do not queue behind each other
+constexpr int NCOMP = 128;  // compute streams: launch groups overlap, so long serial chains do not queue behind each other
 
 struct Stage {
     uint8_t* h = nullptr;  // pinned staging
@@ -629,7 +629,7 @@ int cas_hash_host(cas_ctx* ctx, const void* base, const uint64_t* off, const uin
     if (!uniform || n <= ctx->long_max_objects) {
         const double t_serial = (double)maxlen / 25e6, t_bulk = (double)total / 900e9;
         if (t_serial > 2.0 * t_bulk) {
-            const uint64_t floor_len = std::max<uint64_t>(ctx->long_min_bytes, maxlen / 4);
+            const uint64_t floor_len = std::max<uint64_t>(ctx->long_min_bytes, maxlen / 3);  // lane chains run ~3x slower
             while (n_long < n && n_long < ctx->long_max_objects && len[order[n_long]] >= floor_len) ++n_long;
         }
     }

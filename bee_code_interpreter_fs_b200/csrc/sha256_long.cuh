@@ -28,7 +28,9 @@ __device__ __forceinline__ void sts_v4(uint32_t addr, uint32_t a, uint32_t b, ui
 
 // One round given wk = W[t] + K[t].  ADDS 0: plain adds (ptxas picks IADD3 / IMAD.IADD);
 // 1: shortest dependency chain -- both new values are one 3-input add after Sigma;
-// 2: every add a 2-input add on the FMA pipe.
+// 2: every add a 2-input add on the FMA pipe; 3: the same pipe, but with the data flow
+// rearranged so that both new values are one or two FMA-pipe adds after their Sigma:
+// a' = e' - d + Sigma0 + Maj (minus_one * d on the FMA pipe); 4: as 3 with the last add as IADD3.
 template <int ADDS>
 __device__ __forceinline__ void long_round(uint32_t a, uint32_t b, uint32_t c, uint32_t& d, uint32_t e, uint32_t f,
                                            uint32_t g, uint32_t& h, uint32_t wk, uint32_t one) {
@@ -46,11 +48,21 @@ __device__ __forceinline__ void long_round(uint32_t a, uint32_t b, uint32_t c, u
         const uint32_t p = x + ch + mj;
         d = x2 + ch + s1;
         h = p + s1 + s0;
-    } else {
+    } else if (ADDS == 2) {
         const uint32_t x = fma_add(h, wk, one);
         const uint32_t t1 = fma_add(fma_add(x, ch, one), s1, one);
         d = fma_add(d, t1, one);
         h = fma_add(fma_add(t1, mj, one), s0, one);
+    } else {
+        const uint32_t x2 = fma_add(fma_add(h, wk, one), d, one);  // h + wk + d: all three rounds old
+        const uint32_t m2 = fma_add(d, mj, 0u - one);               // Maj - d   (d * -1 + Maj)
+        const uint32_t dn = fma_add(fma_add(x2, ch, one), s1, one);
+        if (ADDS == 3) {
+            h = fma_add(fma_add(m2, s0, one), dn, one);
+        } else {
+            h = dn + m2 + s0;
+        }
+        d = dn;
     }
 }
 
