@@ -7,14 +7,14 @@ import os
 from ._build import LIB_PATH
 
 CAS_OK = 0
-CAS_E_CUDA, CAS_E_ARG, CAS_E_NOMEM, CAS_E_NODEVICE = -1, -2, -3, -4
+CAS_E_CUDA, CAS_E_ARG, CAS_E_NOMEM, CAS_E_NODEVICE, CAS_E_IO = -1, -2, -3, -4, -5
 OPT_KERNEL, OPT_FMA_LEVEL, OPT_WAVE_BYTES, OPT_PACK_THREADS, OPT_CTAS_PER_SM, OPT_ARENA_BYTES = 1, 2, 3, 4, 5, 6
 OPT_LONG_MAX_OBJECTS, OPT_LONG_MIN_BYTES = 7, 8
 
 # Every symbol include/b200cas.h declares (tests check the library exports them all).
 SYMBOLS = (
     "cas_create", "cas_destroy", "cas_last_error", "cas_set_option", "cas_get_option", "cas_device_info",
-    "cas_hash_host", "cas_hash_device", "cas_hash_device_long", "cas_hash_device_uniform", "cas_gen_synthetic", "cas_int32_peak",
+    "cas_hash_host", "cas_hash_files", "cas_hash_device", "cas_hash_device_long", "cas_hash_device_uniform", "cas_gen_synthetic", "cas_int32_peak",
     "cas_launch_count", "cas_version", "cas_hash_host_static",
 )
 STATIC_MAX_OBJECTS = 1024
@@ -57,6 +57,8 @@ def load() -> ctypes.CDLL:
     lib.cas_device_info.restype = ci
     lib.cas_hash_host.argtypes = [vp, vp, vp, vp, u64, vp]
     lib.cas_hash_host.restype = ci
+    lib.cas_hash_files.argtypes = [vp, vp, u64, vp, vp]
+    lib.cas_hash_files.restype = ci
     lib.cas_hash_device.argtypes = [vp, vp, vp, vp, vp, u64, vp, vp]
     lib.cas_hash_device.restype = ci
     lib.cas_hash_device_long.argtypes = [vp, vp, vp, vp, vp, u64, vp, vp]

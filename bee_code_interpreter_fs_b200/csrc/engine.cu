@@ -14,6 +14,10 @@
 // overlap both later copies and later kernels.  Digests come back once at the end.
 #include <cuda.h>
 #include <cuda_runtime.h>
+#include <errno.h>
+#include <fcntl.h>
+#include <sys/stat.h>
+#include <unistd.h>
 #include <stdint.h>
 #include <stdio.h>
 #include <string.h>
@@ -598,15 +602,38 @@ int cas_int32_peak(cas_ctx* ctx, int mode, int steps, double* lane_ops_per_s, do
     return CAS_OK;
 }
 
-int cas_hash_host(cas_ctx* ctx, const void* base, const uint64_t* off, const uint64_t* len, uint64_t n,
-                  void* out32n) {
-    if (!ctx) return CAS_E_ARG;
-    if (n == 0) return CAS_OK;
-    if (!off || !len || !out32n) return fail(ctx, CAS_E_ARG, "cas_hash_host: NULL offset/length/output array");
-    if (n > 0xFFFFFFFFull) return fail(ctx, CAS_E_ARG, "cas_hash_host: more than 2^32-1 objects in one call");
-    CU(cudaSetDevice(ctx->device));
-    const uint8_t* hbase = static_cast<const uint8_t*>(base);
-    uint8_t* out = static_cast<uint8_t*>(out32n);
+}  // extern "C"
+
+namespace {
+
+// Where the bytes of object i come from: host memory (hbase + off[i]) or a file (paths[i]).
+struct ByteSource {
+    const uint8_t* hbase = nullptr;
+    const uint64_t* off = nullptr;
+    const char* const* paths = nullptr;
+};
+
+// Reads [offset, offset+bytes) of a file into dst; false if the file is shorter or unreadable.
+bool read_file_range(const char* path, uint64_t offset, uint8_t* dst, uint64_t bytes) {
+    const int fd = open(path, O_RDONLY | O_CLOEXEC);
+    if (fd < 0) return false;
+    uint64_t done = 0;
+    while (done < bytes) {
+        const ssize_t r = pread(fd, dst + done, bytes - done, (off_t)(offset + done));
+        if (r <= 0) {
+            if (r < 0 && errno == EINTR) continue;
+            break;
+        }
+        done += (uint64_t)r;
+    }
+    close(fd);
+    return done == bytes;
+}
+
+int hash_host_impl(cas_ctx* ctx, const ByteSource& srcs, const uint64_t* len, uint64_t n, uint8_t* out) {
+    const uint8_t* hbase = srcs.hbase;
+    const uint64_t* off = srcs.off;
+    const bool from_files = srcs.paths != nullptr;
 
     // Schedule: longest first when lengths differ, so that the 32 lanes of a warp
     // carry messages of (nearly) equal block counts and the long chains start early.
@@ -644,7 +671,7 @@ int cas_hash_host(cas_ctx* ctx, const void* base, const uint64_t* off, const uin
     const bool one_epoch = total <= half;
     int rc = ensure_host_path(ctx, one_epoch ? half : 2 * half, chunk, n);
     if (rc) return rc;
-    const bool pinned_src = host_ptr_is_pinned(hbase);
+    const bool pinned_src = !from_files && host_ptr_is_pinned(hbase);
 
     // Device layout in schedule order; epochs are runs of objects that fit one arena half.
     uint64_t* h_off = ctx->h_meta;
@@ -669,7 +696,9 @@ int cas_hash_host(cas_ctx* ctx, const void* base, const uint64_t* off, const uin
     CU(cudaMemcpyAsync(ctx->d_meta + n, h_len, n * 8, cudaMemcpyHostToDevice, ctx->s_copy));
     for (auto& st : ctx->stage) st.used = false;
 
-    struct Piece { const uint8_t* src; uint64_t dst; uint64_t bytes; };
+    // A run of bytes of one object: from memory (src) or from file `obj` at `fpos`.
+    struct Piece { const uint8_t* src; uint64_t dst; uint64_t bytes; uint64_t obj; uint64_t fpos; };
+    std::atomic<bool> io_failed{false};
     std::vector<Piece> pieces;
     uint64_t chunk_no = 0, launch_no = 0;
     for (size_t e = 0; e + 1 < epoch_first.size(); ++e) {
@@ -689,12 +718,16 @@ int cas_hash_host(cas_ctx* ctx, const void* base, const uint64_t* off, const uin
             for (uint64_t k = kp; k < k1 && h_off[k] < c1; ++k) {
                 const uint64_t lo = std::max(h_off[k], c0), hi = std::min(h_off[k] + h_len[k], c1);
                 if (lo >= hi) continue;
+                if (from_files) {
+                    pieces.push_back({nullptr, lo, hi - lo, order[k], lo - h_off[k]});
+                    continue;
+                }
                 const uint8_t* src = hbase + off[order[k]] + (lo - h_off[k]);
                 if (!pieces.empty() && pieces.back().src + pieces.back().bytes == src &&
                     pieces.back().dst + pieces.back().bytes == lo)
                     pieces.back().bytes += hi - lo;
                 else
-                    pieces.push_back({src, lo, hi - lo});
+                    pieces.push_back({src, lo, hi - lo, order[k], 0});
             }
             if (c1 > c0) {
                 if (pinned_src && pieces.size() <= 64) {
@@ -714,9 +747,17 @@ int cas_hash_host(cas_ctx* ctx, const void* base, const uint64_t* off, const uin
                         size_t i = std::partition_point(pv, pv + np, [&](const Piece& q) { return q.dst + q.bytes <= lo; }) - pv;
                         for (; i < np && pv[i].dst < hi; ++i) {
                             const uint64_t a = std::max(pv[i].dst, lo), b = std::min(pv[i].dst + pv[i].bytes, hi);
-                            memcpy(stage + (a - c0), pv[i].src + (a - pv[i].dst), b - a);
+                            if (pv[i].src) {
+                                memcpy(stage + (a - c0), pv[i].src + (a - pv[i].dst), b - a);
+                            } else if (!read_file_range(srcs.paths[pv[i].obj], pv[i].fpos + (a - pv[i].dst), stage + (a - c0), b - a)) {
+                                io_failed.store(true);  // shorter than stat() said, or unreadable
+                            }
                         }
                     });
+                    if (io_failed.load()) {
+                        cudaDeviceSynchronize();
+                        return fail(ctx, CAS_E_IO, "a file changed or could not be read while it was being hashed");
+                    }
                     CU(cudaMemcpyAsync(d_base + c0, stage, span, cudaMemcpyHostToDevice, ctx->s_copy));
                     sg.used = true;
                 }
@@ -761,6 +802,45 @@ int cas_hash_host(cas_ctx* ctx, const void* base, const uint64_t* off, const uin
         for (uint64_t k = 0; k < n; ++k) memcpy(out + 32ull * order[k], ctx->h_dig + 32ull * k, 32);
     }
     return CAS_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int cas_hash_host(cas_ctx* ctx, const void* base, const uint64_t* off, const uint64_t* len, uint64_t n,
+                  void* out32n) {
+    if (!ctx) return CAS_E_ARG;
+    if (n == 0) return CAS_OK;
+    if (!off || !len || !out32n) return fail(ctx, CAS_E_ARG, "cas_hash_host: NULL offset/length/output array");
+    if (n > 0xFFFFFFFFull) return fail(ctx, CAS_E_ARG, "cas_hash_host: more than 2^32-1 objects in one call");
+    CU(cudaSetDevice(ctx->device));
+    ByteSource src;
+    src.hbase = static_cast<const uint8_t*>(base);
+    src.off = off;
+    return hash_host_impl(ctx, src, len, n, static_cast<uint8_t*>(out32n));
+}
+
+int cas_hash_files(cas_ctx* ctx, const char* const* paths, uint64_t n, void* out32n, uint64_t* sizes_out) {
+    if (!ctx) return CAS_E_ARG;
+    if (n == 0) return CAS_OK;
+    if (!paths || !out32n) return fail(ctx, CAS_E_ARG, "cas_hash_files: NULL path or output array");
+    if (n > 0xFFFFFFFFull) return fail(ctx, CAS_E_ARG, "cas_hash_files: more than 2^32-1 files in one call");
+    CU(cudaSetDevice(ctx->device));
+    std::vector<uint64_t> len(n);
+    for (uint64_t i = 0; i < n; ++i) {
+        struct stat sb;
+        if (!paths[i] || stat(paths[i], &sb) != 0 || !S_ISREG(sb.st_mode)) {
+            char msg[400];
+            snprintf(msg, sizeof msg, "cas_hash_files: cannot stat regular file '%.300s'", paths[i] ? paths[i] : "(null)");
+            return fail(ctx, CAS_E_IO, msg);
+        }
+        len[i] = (uint64_t)sb.st_size;
+    }
+    if (sizes_out) memcpy(sizes_out, len.data(), n * sizeof(uint64_t));
+    ByteSource src;
+    src.paths = paths;
+    return hash_host_impl(ctx, src, len.data(), n, static_cast<uint8_t*>(out32n));
 }
 
 // ---------------------------------------------------------------------------

@@ -7,6 +7,7 @@ PyTorch is used only for device buffers and stream handles.
 from __future__ import annotations
 
 import ctypes
+import os
 import threading
 from typing import Sequence
 
@@ -134,6 +135,24 @@ class GpuHasher:
     def hash_many(self, objs: Sequence[BytesLike]) -> list[str]:
         """Object ids (64 lowercase hex characters) of a batch of objects."""
         return [row.tobytes().hex() for row in self.digest_many(objs)]
+
+    def digest_files(self, paths: Sequence[str | os.PathLike]) -> tuple[np.ndarray, np.ndarray]:
+        """((n, 32) digests, sizes) of files, read straight into pinned staging by the engine."""
+        n = len(paths)
+        out = np.empty((n, 32), dtype=np.uint8)
+        sizes = np.zeros(n, dtype=np.uint64)
+        if n == 0:
+            return out, sizes
+        raw = [os.fsencode(p) for p in paths]
+        arr = (ctypes.c_char_p * n)(*raw)
+        with self._lock:
+            self._check(self._lib.cas_hash_files(self._ctx, ctypes.cast(arr, ctypes.c_void_p), n, out.ctypes.data,
+                                                 sizes.ctypes.data))
+        return out, sizes
+
+    def hash_files(self, paths: Sequence[str | os.PathLike]) -> list[str]:
+        """Object ids of files on disk (the store directory, a workspace)."""
+        return [row.tobytes().hex() for row in self.digest_files(paths)[0]]
 
     def hash_one(self, data: BytesLike) -> str:
         return self.hash_many([data])[0]

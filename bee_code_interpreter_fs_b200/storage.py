@@ -13,6 +13,10 @@ Consequences of content-derived ids:
   (services/kubernetes_code_executor.py:146);
 * equal content gives equal ids: a second write of the same bytes is a no-op.
 
+* ``delete`` removes the file, as in the reference; because equal content now shares
+  one file, ``Storage(..., refcount=True)`` keeps a per-object holder count instead
+  (one ``write`` = one holder) and only the last ``delete`` unlinks.
+
 Concurrent finalisations (the ``asyncio.gather`` over changed files at
 kubernetes_code_executor.py:149-154) are coalesced into one GPU batch by
 ``_Batcher``; the blocking CUDA call runs in a worker thread, off the event loop.
@@ -119,11 +123,28 @@ class Storage:
     """
 
     def __init__(self, storage_path: str, hasher=None, device: int = 0, batch_window: float = 0.002,
-                 max_batch: int = 4096):
+                 max_batch: int = 4096, refcount: bool = False):
         self.storage_path = Path(storage_path)
         # No fallback: if the CUDA library or a B200 is missing this raises.
         self._hasher = hasher if hasher is not None else GpuHasher(device)
         self._batcher = _Batcher(self._hasher, batch_window, max_batch)
+        self._refcount = refcount
+        self._ref_lock: asyncio.Lock | None = None
+
+    # -- holder counts (only with refcount=True) -------------------------------------------
+    def _refs_path(self, object_id: str) -> Path:
+        return self.storage_path / f".refs-{object_id}"  # '.' cannot occur in an id (validation.Hash)
+
+    async def _read_refs(self, object_id: str) -> int:
+        try:
+            return int((await self._refs_path(object_id).read_text()).strip() or 0)
+        except (FileNotFoundError, ValueError):
+            return 1 if await (self.storage_path / object_id).exists() else 0
+
+    def _lock_refs(self) -> asyncio.Lock:
+        if self._ref_lock is None:
+            self._ref_lock = asyncio.Lock()
+        return self._ref_lock
 
     @property
     def hasher(self):
@@ -135,6 +156,16 @@ class Storage:
 
     async def _publish(self, tmp: Path, object_id: str) -> None:
         target = self.storage_path / object_id
+        if self._refcount:
+            async with self._lock_refs():
+                holders = await self._read_refs(object_id) if await target.exists() else 0
+                await self._publish_file(tmp, target)
+                await self._refs_path(object_id).write_text(str(holders + 1))
+        else:
+            await self._publish_file(tmp, target)
+
+    @staticmethod
+    async def _publish_file(tmp: Path, target: Path) -> None:
         if await target.exists():
             await tmp.unlink(missing_ok=True)  # same content already stored
         else:
@@ -182,7 +213,7 @@ class Storage:
         ids = await self.hash_many(objects)
         await self.storage_path.mkdir(parents=True, exist_ok=True)
         for data, object_id in zip(objects, ids):
-            if await (self.storage_path / object_id).exists():
+            if not self._refcount and await (self.storage_path / object_id).exists():
                 continue
             tmp = self.storage_path / f".tmp-{secrets.token_hex(16)}"
             try:
@@ -226,15 +257,39 @@ class Storage:
         Delete an object with the given hash from the storage.
         """
         file_path = self.storage_path / object_hash
-        if await file_path.exists():
-            await file_path.unlink()
-        else:
+        if not await file_path.exists():
             raise FileNotFoundError(f"File not found: {object_hash}")
+        if self._refcount:
+            async with self._lock_refs():
+                holders = await self._read_refs(object_hash) - 1
+                if holders > 0:  # another writer of the same content still holds it
+                    await self._refs_path(object_hash).write_text(str(holders))
+                    return
+                await self._refs_path(object_hash).unlink(missing_ok=True)
+                await file_path.unlink()
+        else:
+            await file_path.unlink()
 
     async def verify(self, object_hashes: Sequence[str]) -> dict[str, bool]:
-        """Re-hashes stored objects in one GPU batch: id -> (content still matches id)."""
+        """Re-hashes stored objects in one GPU batch: id -> (content still matches id).
+        With a GPU hasher the engine reads the files itself (cas_hash_files: pread into
+        pinned staging), so the bytes never pass through Python."""
         present = [h for h in object_hashes if await self.exists(h)]
-        blobs = [await (self.storage_path / h).read_bytes() for h in present]
-        ids = await self.hash_many(blobs)
+        loop = asyncio.get_running_loop()
+        if hasattr(self._hasher, "hash_files"):
+            paths = [str(self.storage_path / h) for h in present]
+            ids = await loop.run_in_executor(None, self._hasher.hash_files, paths) if paths else []
+        else:
+            blobs = [await (self.storage_path / h).read_bytes() for h in present]
+            ids = await self.hash_many(blobs)
         ok = {h: (h == got) for h, got in zip(present, ids)}
         return {h: ok.get(h, False) for h in object_hashes}
+
+    async def verify_all(self) -> dict[str, bool]:
+        """Integrity scrub of the whole store directory (temporary and holder-count files skipped)."""
+        names = []
+        if await self.storage_path.exists():
+            async for entry in self.storage_path.iterdir():
+                if not entry.name.startswith(".") and await entry.is_file():
+                    names.append(entry.name)
+        return await self.verify(sorted(names))

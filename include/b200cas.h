@@ -35,6 +35,7 @@ extern "C" {
 #define CAS_E_ARG (-2)      /* invalid argument */
 #define CAS_E_NOMEM (-3)    /* host or device allocation failed */
 #define CAS_E_NODEVICE (-4) /* no CUDA device / wrong architecture */
+#define CAS_E_IO (-5)       /* a file could not be read (cas_hash_files) */
 
 typedef struct cas_ctx cas_ctx;
 
@@ -76,6 +77,17 @@ int cas_device_info(const cas_ctx* ctx, int* sm_count, int* sm_clock_khz, uint64
  */
 int cas_hash_host(cas_ctx* ctx, const void* base, const uint64_t* off, const uint64_t* len, uint64_t n,
                   void* out32n);
+
+/*
+ * Ids of objects that live in FILES: the store directory itself (one file per object,
+ * storage.py:53, :69-75) or a workspace about to be stored.  Same pipeline as
+ * cas_hash_host, except that the pinned staging is filled by pread() from a few host
+ * threads, so file bytes go disk/page cache -> pinned memory -> GPU without an
+ * intermediate copy.  sizes_out (may be NULL) receives the file sizes.  A file that is
+ * missing, not regular, or changes size during the call fails the call with CAS_E_IO.
+ * Serves Storage.verify (an integrity scrub of the store) and bulk imports.
+ */
+int cas_hash_files(cas_ctx* ctx, const char* const* paths, uint64_t n, void* out32n, uint64_t* sizes_out);
 
 /*
  * Same arithmetic for objects already resident in DEVICE memory (kernel only,

@@ -174,6 +174,34 @@ def test_write_many_and_verify(tmp_path, oracle_hasher):
     run(go())
 
 
+def test_refcounted_delete_keeps_shared_content(tmp_path, oracle_hasher):
+    """Equal content shares one file; with refcount=True only the last holder's delete unlinks."""
+
+    async def go():
+        st = Storage(str(tmp_path), hasher=oracle_hasher, refcount=True)
+        a = await st.write(b"shared")
+        b = await st.write(b"shared")
+        (c,) = await st.write_many([b"shared"])
+        assert a == b == c
+        await st.delete(a)
+        await st.delete(a)
+        assert await st.exists(a) and await st.read(a) == b"shared"
+        await st.delete(a)
+        assert not await st.exists(a)
+        with pytest.raises(FileNotFoundError):
+            await st.delete(a)
+        assert await st.verify_all() == {}
+        # default (reference) semantics: the first delete removes the object
+        plain = Storage(str(tmp_path / "plain"), hasher=oracle_hasher)
+        x = await plain.write(b"shared")
+        await plain.write(b"shared")
+        await plain.delete(x)
+        assert not await plain.exists(x)
+
+    run(go())
+    assert [n for n in os.listdir(tmp_path) if n != "plain"] == []
+
+
 def test_engine_failure_reaches_the_caller(tmp_path):
     class Broken:
         def hash_many(self, objs):
