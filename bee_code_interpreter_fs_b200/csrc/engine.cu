@@ -656,7 +656,7 @@ int hash_host_impl(cas_ctx* ctx, const ByteSource& srcs, const uint64_t* len, ui
     if (!uniform || n <= ctx->long_max_objects) {
         const double t_serial = (double)maxlen / 25e6, t_bulk = (double)total / 900e9;
         if (t_serial > 2.0 * t_bulk) {
-            const uint64_t floor_len = std::max<uint64_t>(ctx->long_min_bytes, maxlen / 3);  // lane chains run ~3x slower
+            const uint64_t floor_len = std::max<uint64_t>(ctx->long_min_bytes, maxlen / 4);  // measured better than /3 on config 4
             while (n_long < n && n_long < ctx->long_max_objects && len[order[n_long]] >= floor_len) ++n_long;
         }
     }

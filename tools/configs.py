@@ -131,7 +131,7 @@ def c4(h):
     res.update({"kernel_ms_unsorted": ms2, "kernel_gb_s_unsorted": total / ms2 / 1e6})
     # the hybrid the host path uses: the longest objects one warp each, the rest one lane each
     srt = np.argsort(-lengths.astype(np.int64), kind="stable")
-    n_long = int((lengths >= max(32768, int(lengths.max()) // 3)).sum())
+    n_long = int((lengths >= max(32768, int(lengths.max()) // 4)).sum())
     o_long = torch.from_numpy(srt[:n_long].astype(np.int32)).cuda()
     o_rest = torch.from_numpy(srt[n_long:].astype(np.int32)).cuda()
     s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
