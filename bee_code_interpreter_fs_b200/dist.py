@@ -87,3 +87,32 @@ def gather_digests(local: np.ndarray, counts: list[int]) -> np.ndarray:
     parts = [torch.empty_like(pad) for _ in range(world)]
     dist.all_gather(parts, pad)
     return np.concatenate([p[:c].cpu().numpy() for p, c in zip(parts, counts)], axis=0)
+
+
+def bind_to_gpu_numa_node(local_rank: int) -> dict:
+    """Pins this process to the CPUs of the NUMA node its GPU hangs off, so that pinned
+    staging is allocated next to the GPU's PCIe root.  No-op (and says so) when the
+    platform hides the topology, as most virtual machines do."""
+    import torch
+
+    info = {"numa_node": None, "cpus": None}
+    try:
+        p = torch.cuda.get_device_properties(local_rank)
+        bdf = f"{p.pci_domain_id:04x}:{p.pci_bus_id:02x}:{p.pci_device_id:02x}.0"
+        with open(f"/sys/bus/pci/devices/{bdf}/numa_node") as f:
+            node = int(f.read().strip())
+        info["numa_node"] = node
+        if node < 0:
+            return info
+        with open(f"/sys/devices/system/node/node{node}/cpulist") as f:
+            cpus = set()
+            for part in f.read().strip().split(","):
+                lo, _, hi = part.partition("-")
+                cpus.update(range(int(lo), int(hi or lo) + 1))
+        allowed = cpus & set(os.sched_getaffinity(0))
+        if allowed:
+            os.sched_setaffinity(0, allowed)
+            info["cpus"] = len(allowed)
+    except (OSError, ValueError, AttributeError):
+        pass
+    return info
