@@ -43,6 +43,26 @@ def log(*a):
     print(*a, file=sys.stderr, flush=True)
 
 
+# stdout carries exactly one JSON line.  Libraries print banners there too (NCCL's version
+# line on rank 0, for one), so file descriptor 1 points at stderr while the run is in
+# progress and the line is written to the saved descriptor at the end.
+_REAL_STDOUT = None
+
+
+def capture_stdout() -> None:
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line: dict) -> None:
+    data = (json.dumps(line) + "\n").encode()
+    sys.stdout.flush()
+    os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, data)
+
+
 def nblocks(length: int) -> int:
     return (length + 9 + 63) // 64
 
@@ -184,7 +204,7 @@ def run_reference(args) -> None:
                                    np.full(min(sample, 256), length, dtype=np.uint64))
     assert port[0].tobytes() == want0
     desc = f"{sample} of {args.objects} objects x {length} B per step, hashlib.sha256 on {cores} threads"
-    print(json.dumps({
+    emit({
         "impl": "reference", "metric": "sha256_gb_per_s", "value": gbs, "unit": "GB/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
@@ -192,7 +212,7 @@ def run_reference(args) -> None:
         "cpu_baseline": {"value": gbs, "unit": "GB/s", "cores": cores, "kind": "reference", "sample": desc},
         "e2e": {"value": gbs, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
-    }), flush=True)
+    })
 
 
 def workload_config(args, world: int) -> dict:
@@ -406,7 +426,7 @@ def run_ours(args) -> None:
     }
     if cpu:
         line["cpu_baseline"] = cpu
-    print(json.dumps(line), flush=True)
+    emit(line)
     h.close()
 
 
@@ -428,6 +448,7 @@ def main() -> None:
     ap.add_argument("--ref-sample-bytes", type=float, default=float(2 << 30))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
+    capture_stdout()
     if args.warmup < 3 and args.impl == "ours":
         log("[warn] fewer than 3 warm-up steps breaks the timing rules")
     if args.impl == "reference":
