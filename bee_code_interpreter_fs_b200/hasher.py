@@ -19,16 +19,24 @@ from ._ffi import CasError
 BytesLike = bytes | bytearray | memoryview | np.ndarray
 
 
+def hex_ids(digests: np.ndarray) -> list[str]:
+    """64-character lowercase hex ids of an (n, 32) digest array (one hex() call, then slices)."""
+    flat = np.ascontiguousarray(digests, dtype=np.uint8).tobytes().hex()
+    return [flat[i:i + 64] for i in range(0, len(flat), 64)]
+
+
 def _addresses(objs: Sequence[BytesLike]) -> tuple[np.ndarray, np.ndarray, list]:
     """Host addresses and lengths of the objects, without copying them."""
     n = len(objs)
-    length = np.fromiter((len(o) if not isinstance(o, np.ndarray) else o.nbytes for o in objs), dtype=np.uint64, count=n)
     keep: list = []
-    if all(type(o) is bytes for o in objs):
+    if set(map(type, objs)) <= {bytes}:
+        length = np.fromiter(map(len, objs), dtype=np.uint64, count=n)
         arr = (ctypes.c_char_p * n)(*objs)  # pointers into the bytes objects themselves
         addr = np.frombuffer(arr, dtype=np.uint64, count=n).copy() if n else np.zeros(0, np.uint64)
         keep.append(arr)
     else:
+        length = np.fromiter((len(o) if not isinstance(o, np.ndarray) else o.nbytes for o in objs), dtype=np.uint64,
+                             count=n)
         addr = np.zeros(n, dtype=np.uint64)
         for i, o in enumerate(objs):
             if isinstance(o, np.ndarray):
@@ -134,7 +142,7 @@ class GpuHasher:
 
     def hash_many(self, objs: Sequence[BytesLike]) -> list[str]:
         """Object ids (64 lowercase hex characters) of a batch of objects."""
-        return [row.tobytes().hex() for row in self.digest_many(objs)]
+        return hex_ids(self.digest_many(objs))
 
     def digest_files(self, paths: Sequence[str | os.PathLike]) -> tuple[np.ndarray, np.ndarray]:
         """((n, 32) digests, sizes) of files, read straight into pinned staging by the engine."""
@@ -152,7 +160,7 @@ class GpuHasher:
 
     def hash_files(self, paths: Sequence[str | os.PathLike]) -> list[str]:
         """Object ids of files on disk (the store directory, a workspace)."""
-        return [row.tobytes().hex() for row in self.digest_files(paths)[0]]
+        return hex_ids(self.digest_files(paths)[0])
 
     def hash_one(self, data: BytesLike) -> str:
         return self.hash_many([data])[0]
@@ -260,4 +268,4 @@ class MultiGpuHasher:
         return shard.scatter_back(parts, results, n)
 
     def hash_many(self, objs: Sequence[BytesLike]) -> list[str]:
-        return [row.tobytes().hex() for row in self.digest_many(objs)]
+        return hex_ids(self.digest_many(objs))

@@ -15,7 +15,7 @@ import numpy as np
 
 from . import _ffi
 from ._ffi import STATIC_MAX_BYTES, STATIC_MAX_OBJECTS, CasError  # noqa: F401  (re-exported limits)
-from .hasher import _addresses
+from .hasher import _addresses, hex_ids
 
 
 def digest_many_static(objs, device: int = 0, stream: int = 0) -> np.ndarray:
@@ -35,4 +35,4 @@ def digest_many_static(objs, device: int = 0, stream: int = 0) -> np.ndarray:
 
 def hash_many_static(objs, device: int = 0, stream: int = 0) -> list[str]:
     """Object ids (64 hex characters) of a small batch; see ``digest_many_static``."""
-    return [row.tobytes().hex() for row in digest_many_static(objs, device, stream)]
+    return hex_ids(digest_many_static(objs, device, stream))
