@@ -244,6 +244,53 @@ def test_full_size_4k_config_sampled_and_cross_checked(hasher):
     assert sums[0] == sums[1] == sums[2]
 
 
+def test_full_size_64k_config_cross_checked(hasher):
+    """BASELINE config 3 at full size (2^20 x 64 KiB = 64 GiB): the TMA-tile kernel and the
+    per-lane-load kernel must agree on every one of the 2^20 digests (checksum of checksums),
+    and a seeded sample is compared with the oracle."""
+    free, _ = torch.cuda.mem_get_info(0)
+    n, length = 1 << 20, 65536
+    if free < n * length + (4 << 30):
+        pytest.skip("not enough free device memory for the 64 GiB batch")
+    buf = torch.empty(n * length, dtype=torch.uint8, device="cuda:0")
+    hasher.gen_synthetic(buf, 0xB200, 0, n, length)
+    sums = {}
+    for kernel in (2, 0):
+        configure(hasher, kernel)
+        dig = hasher.digest_device_uniform(buf, length, length, n)
+        torch.cuda.synchronize()
+        host = dig.cpu().numpy()
+        sums[kernel] = hashlib.sha256(host.tobytes()).hexdigest()
+        if kernel == 2:
+            rng = np.random.default_rng(2)
+            for i in [0, 31, 32, 255, 256, n - 1] + rng.integers(0, n, size=250).tolist():
+                assert bytes(host[i]).hex() == hashlib.sha256(oracle.synth_object(0xB200, i, length)).hexdigest()
+    assert sums[2] == sums[0]
+    del buf
+
+
+def test_c_abi_rejects_bad_arguments_with_a_message(hasher):
+    """Errors are codes plus text, never a placeholder digest (include/b200cas.h conventions)."""
+    from bee_code_interpreter_fs_b200 import CasError
+
+    buf = torch.zeros(4096, dtype=torch.uint8, device="cuda:0")
+    with pytest.raises(CasError, match="stride smaller than length"):
+        hasher.digest_device_uniform(buf, 16, 64, 4)
+    with pytest.raises(CasError, match="CAS_OPT_FMA_LEVEL"):
+        hasher.set_option(_ffi.OPT_FMA_LEVEL, 9)
+    with pytest.raises(CasError, match="unknown option"):
+        hasher.set_option(99, 1)
+    with pytest.raises(ValueError):
+        hasher.digest_packed(None, np.zeros(3, np.uint64), np.zeros(2, np.uint64))
+    with pytest.raises(ValueError, match="too small"):
+        hasher.gen_synthetic(buf, 1, 0, 100, 4096)
+    lib = _ffi.load()
+    assert lib.cas_hash_host(hasher._ctx, None, None, None, 5, None) == _ffi.CAS_E_ARG
+    assert b"NULL" in lib.cas_last_error(hasher._ctx)
+    assert lib.cas_hash_host(hasher._ctx, None, None, None, 0, None) == _ffi.CAS_OK  # empty batch is fine
+    assert hasher.hash_many([b"still works"]) == [hashlib.sha256(b"still works").hexdigest()]
+
+
 def test_digests_independent_of_batch_position_and_neighbours(hasher):
     """Idempotence / independence: an object's id does not depend on which lane or warp hashed it."""
     rng = np.random.default_rng(3)
