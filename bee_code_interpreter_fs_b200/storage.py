@@ -17,6 +17,9 @@ Consequences of content-derived ids:
   one file, ``Storage(..., refcount=True)`` keeps a per-object holder count instead
   (one ``write`` = one holder) and only the last ``delete`` unlinks.
 
+With the GPU hasher a streaming writer keeps nothing in memory: chunks go to the spool file and
+the engine reads that file itself at close (``cas_hash_files``: pread into pinned staging).
+
 Concurrent finalisations (the ``asyncio.gather`` over changed files at
 kubernetes_code_executor.py:149-154) are coalesced into one GPU batch by
 ``_Batcher``; the blocking CUDA call runs in a worker thread, off the event loop.
@@ -48,22 +51,34 @@ class ObjectWriter(Protocol):
 
 
 class _Batcher:
-    """Collects ``hash(data)`` requests that arrive within ``window`` seconds of
-    each other (or until ``max_batch`` are waiting) and hashes them in one call."""
+    """Collects id requests that arrive within ``window`` seconds of each other (or until
+    ``max_batch`` are waiting) and hashes them in one engine call.  A request is either
+    bytes in memory (``hash``) or a file the engine reads itself (``hash_path``, only with
+    a hasher that offers ``hash_files``); a mixed batch costs one call per kind."""
 
     def __init__(self, hasher, window: float, max_batch: int):
         self._hasher = hasher
         self._window = window
         self._max_batch = max_batch
-        self._pending: list[tuple[bytes, asyncio.Future]] = []
+        self._pending: list[tuple[bytes | str, bool, asyncio.Future]] = []  # (payload, is_path, future)
         self._timer: asyncio.TimerHandle | None = None
         self._lock: asyncio.Lock | None = None
         self.batches = 0  # number of GPU batches issued (observable in tests)
 
+    @property
+    def reads_files(self) -> bool:
+        return hasattr(self._hasher, "hash_files")
+
     async def hash(self, data: bytes) -> str:
+        return await self._submit(data, False)
+
+    async def hash_path(self, path: str) -> str:
+        return await self._submit(path, True)
+
+    async def _submit(self, payload, is_path: bool) -> str:
         loop = asyncio.get_running_loop()
         fut: asyncio.Future = loop.create_future()
-        self._pending.append((data, fut))
+        self._pending.append((payload, is_path, fut))
         if len(self._pending) >= self._max_batch:
             self._fire(loop)
         elif self._timer is None:
@@ -78,20 +93,28 @@ class _Batcher:
         if batch:
             loop.create_task(self._run(batch))
 
-    async def _run(self, batch: list[tuple[bytes, asyncio.Future]]) -> None:
+    def _hash_batch(self, batch) -> list[str]:
+        """Worker thread: one engine call per kind of payload, ids back in request order."""
+        ids: list = [None] * len(batch)
+        for want_path, fn in ((False, getattr(self._hasher, "hash_many")), (True, getattr(self._hasher, "hash_files", None))):
+            idx = [i for i, (_, is_path, _f) in enumerate(batch) if is_path == want_path]
+            if idx:
+                for i, object_id in zip(idx, fn([batch[i][0] for i in idx])):
+                    ids[i] = object_id
+        return ids
+
+    async def _run(self, batch) -> None:
         if self._lock is None:
             self._lock = asyncio.Lock()
         try:
             async with self._lock:  # one batch on the device context at a time
                 self.batches += 1
-                ids = await asyncio.get_running_loop().run_in_executor(
-                    None, self._hasher.hash_many, [d for d, _ in batch]
-                )
-            for (_, fut), object_id in zip(batch, ids):
+                ids = await asyncio.get_running_loop().run_in_executor(None, self._hash_batch, batch)
+            for (_, _p, fut), object_id in zip(batch, ids):
                 if not fut.done():
                     fut.set_result(object_id)
         except BaseException as e:  # noqa: BLE001 - an engine failure must reach every waiter
-            for _, fut in batch:
+            for _, _p, fut in batch:
                 if not fut.done():
                     fut.set_exception(e if isinstance(e, Exception) else RuntimeError(str(e)))
             if not isinstance(e, Exception):
@@ -99,16 +122,18 @@ class _Batcher:
 
 
 class _SpoolWriter:
-    """What ``Storage.writer()`` yields: ``write`` appends a chunk, ``hash`` is set on close."""
+    """What ``Storage.writer()`` yields: ``write`` appends a chunk, ``hash`` is set on close.
+    Chunks are kept in memory only when the hasher cannot read the spooled file itself."""
 
-    def __init__(self, file):
+    def __init__(self, file, keep_chunks: bool):
         self._file = file
-        self._chunks: list[bytes] = []
+        self._chunks: list[bytes] | None = [] if keep_chunks else None
         self.hash: str = ""
 
     async def write(self, data: bytes) -> None:
         data = bytes(data)
-        self._chunks.append(data)
+        if self._chunks is not None:
+            self._chunks.append(data)
         await self._file.write(data)
 
     def _content(self) -> bytes:
@@ -182,13 +207,17 @@ class Storage:
         await self.storage_path.mkdir(parents=True, exist_ok=True)
         tmp = self.storage_path / f".tmp-{secrets.token_hex(16)}"
         file = await tmp.open("wb")
-        spool = _SpoolWriter(file)
+        from_file = self._batcher.reads_files  # the engine preads the spooled file: O(1) memory per writer
+        spool = _SpoolWriter(file, keep_chunks=not from_file)
         try:
             try:
                 yield spool
             finally:
                 await file.aclose()
-            spool.hash = await self._batcher.hash(spool._content())
+            if from_file:
+                spool.hash = await self._batcher.hash_path(str(tmp))
+            else:
+                spool.hash = await self._batcher.hash(spool._content())
             await self._publish(tmp, spool.hash)
         except BaseException:
             await tmp.unlink(missing_ok=True)

@@ -78,6 +78,25 @@ class OracleHasher:
         return np.frombuffer(b"".join(sha256_oracle.hashlib_digests(objs)), dtype=np.uint8).reshape(-1, 32)
 
 
+class OracleFileHasher(OracleHasher):
+    """Same, but also able to hash files by path, like GpuHasher.hash_files."""
+
+    def __init__(self):
+        super().__init__()
+        self.file_calls = 0
+
+    def hash_files(self, paths):
+        from oracle import sha256_oracle
+
+        self.file_calls += 1
+        return [d.hex() for d in sha256_oracle.hashlib_digests([open(p, "rb").read() for p in paths])]
+
+
 @pytest.fixture
 def oracle_hasher():
     return OracleHasher()
+
+
+@pytest.fixture
+def oracle_file_hasher():
+    return OracleFileHasher()

@@ -160,6 +160,31 @@ def test_concurrent_finalisations_coalesce_into_one_batch(tmp_path, oracle_hashe
         assert object_id == hashlib.sha256(b"chunk-%d-" % i + b"x" * i).hexdigest()
 
 
+def test_streaming_writers_are_hashed_from_their_spool_files(tmp_path, oracle_file_hasher):
+    """With a hasher that reads files (GpuHasher.hash_files) a writer keeps no chunk in memory."""
+
+    async def go():
+        st = Storage(str(tmp_path), hasher=oracle_file_hasher, batch_window=0.05)
+
+        async def download(i):
+            async with st.writer() as f:
+                assert f._chunks is None
+                for k in range(3):
+                    await f.write(b"%d-%d;" % (i, k) * 1000)
+            return f.hash
+
+        ids = await asyncio.gather(*(download(i) for i in range(8)), st.hash_many([b"in memory"]))
+        return st, ids
+
+    st, ids = run(go())
+    assert oracle_file_hasher.file_calls == 1 and st.gpu_batches == 1  # eight spool files, one engine call
+    for i in range(8):
+        want = hashlib.sha256(b"".join(b"%d-%d;" % (i, k) * 1000 for k in range(3))).hexdigest()
+        assert ids[i] == want and (tmp_path / want).read_bytes().startswith(b"%d-0;" % i)
+    assert ids[8] == [hashlib.sha256(b"in memory").hexdigest()]
+    assert sorted(os.listdir(tmp_path)) == sorted(ids[:8])
+
+
 def test_write_many_and_verify(tmp_path, oracle_hasher):
     async def go():
         st = Storage(str(tmp_path), hasher=oracle_hasher)
