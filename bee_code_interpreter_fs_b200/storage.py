@@ -29,6 +29,7 @@ from __future__ import annotations
 
 import asyncio
 import os
+import re
 import secrets
 from contextlib import asynccontextmanager
 from typing import AsyncIterator, Protocol, Sequence
@@ -37,7 +38,9 @@ from anyio import Path
 from pydantic import validate_call
 
 from .hasher import GpuHasher
-from .validation import Hash
+from .validation import HASH_PATTERN, Hash
+
+_ID_RE = re.compile(HASH_PATTERN)
 
 
 class ObjectReader(Protocol):
@@ -237,20 +240,44 @@ class Storage:
             return []
         return await asyncio.get_running_loop().run_in_executor(None, self._hasher.hash_many, list(objects))
 
-    async def write_many(self, objects: Sequence[bytes]) -> list[str]:
-        """Stores a batch of objects and returns their ids (one GPU batch)."""
-        ids = await self.hash_many(objects)
-        await self.storage_path.mkdir(parents=True, exist_ok=True)
+    def _store_batch_sync(self, objects: Sequence[bytes], ids: Sequence[str]) -> None:
+        """Worker thread: write every object of a batch that is not stored yet (temp name, then
+        rename), with plain os calls -- one thread hop for the batch instead of four per object."""
+        root = str(self.storage_path)
+        os.makedirs(root, exist_ok=True)
         for data, object_id in zip(objects, ids):
-            if not self._refcount and await (self.storage_path / object_id).exists():
-                continue
-            tmp = self.storage_path / f".tmp-{secrets.token_hex(16)}"
-            try:
-                await tmp.write_bytes(data)
-                await self._publish(tmp, object_id)
-            except BaseException:
-                await tmp.unlink(missing_ok=True)
-                raise
+            target = os.path.join(root, object_id)
+            present = os.path.exists(target)
+            if not present:
+                tmp = os.path.join(root, f".tmp-{secrets.token_hex(16)}")
+                try:
+                    with open(tmp, "wb") as f:
+                        f.write(data)
+                    os.rename(tmp, target)
+                except BaseException:
+                    if os.path.exists(tmp):
+                        os.unlink(tmp)
+                    raise
+            if self._refcount:
+                refs = os.path.join(root, f".refs-{object_id}")
+                try:
+                    holders = int(open(refs).read().strip() or 0)
+                except (FileNotFoundError, ValueError):
+                    holders = 1 if present else 0
+                with open(refs, "w") as f:
+                    f.write(str(holders + 1))
+
+    async def write_many(self, objects: Sequence[bytes]) -> list[str]:
+        """Stores a batch of objects and returns their ids: one GPU batch, one worker-thread
+        hop for all the file writes."""
+        objects = list(objects)
+        ids = await self.hash_many(objects)
+        loop = asyncio.get_running_loop()
+        if self._refcount:
+            async with self._lock_refs():  # holder counts are read-modify-write
+                await loop.run_in_executor(None, self._store_batch_sync, objects, ids)
+        else:
+            await loop.run_in_executor(None, self._store_batch_sync, objects, ids)
         return ids
 
     @asynccontextmanager
@@ -299,26 +326,38 @@ class Storage:
         else:
             await file_path.unlink()
 
-    async def verify(self, object_hashes: Sequence[str]) -> dict[str, bool]:
-        """Re-hashes stored objects in one GPU batch: id -> (content still matches id).
-        With a GPU hasher the engine reads the files itself (cas_hash_files: pread into
-        pinned staging), so the bytes never pass through Python."""
-        present = [h for h in object_hashes if await self.exists(h)]
-        loop = asyncio.get_running_loop()
+    def _verify_sync(self, object_hashes: Sequence[str]) -> dict[str, bool]:
+        root = str(self.storage_path)
+        present = [h for h in object_hashes if os.path.isfile(os.path.join(root, h))]
         if hasattr(self._hasher, "hash_files"):
-            paths = [str(self.storage_path / h) for h in present]
-            ids = await loop.run_in_executor(None, self._hasher.hash_files, paths) if paths else []
+            ids = self._hasher.hash_files([os.path.join(root, h) for h in present]) if present else []
         else:
-            blobs = [await (self.storage_path / h).read_bytes() for h in present]
-            ids = await self.hash_many(blobs)
+            blobs = []
+            for h in present:
+                with open(os.path.join(root, h), "rb") as f:
+                    blobs.append(f.read())
+            ids = self._hasher.hash_many(blobs) if blobs else []
         ok = {h: (h == got) for h, got in zip(present, ids)}
         return {h: ok.get(h, False) for h in object_hashes}
 
+    async def verify(self, object_hashes: Sequence[str]) -> dict[str, bool]:
+        """Re-hashes stored objects in one GPU batch: id -> (content still matches id).
+        With a GPU hasher the engine reads the files itself (cas_hash_files: pread into
+        pinned staging), so the bytes never pass through Python; the whole check is one
+        worker-thread hop."""
+        for h in object_hashes:
+            if not _ID_RE.fullmatch(h):
+                raise ValueError(f"not an object id: {h!r}")
+        return await asyncio.get_running_loop().run_in_executor(None, self._verify_sync, list(object_hashes))
+
     async def verify_all(self) -> dict[str, bool]:
         """Integrity scrub of the whole store directory (temporary and holder-count files skipped)."""
-        names = []
-        if await self.storage_path.exists():
-            async for entry in self.storage_path.iterdir():
-                if not entry.name.startswith(".") and await entry.is_file():
-                    names.append(entry.name)
-        return await self.verify(sorted(names))
+
+        def scan() -> dict[str, bool]:
+            root = str(self.storage_path)
+            if not os.path.isdir(root):
+                return {}
+            names = sorted(e.name for e in os.scandir(root) if not e.name.startswith(".") and e.is_file())
+            return self._verify_sync(names)
+
+        return await asyncio.get_running_loop().run_in_executor(None, scan)
