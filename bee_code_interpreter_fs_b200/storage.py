@@ -158,6 +158,7 @@ class Storage:
         self._batcher = _Batcher(self._hasher, batch_window, max_batch)
         self._refcount = refcount
         self._ref_lock: asyncio.Lock | None = None
+        self._dir_ready = False
 
     # -- holder counts (only with refcount=True) -------------------------------------------
     def _refs_path(self, object_id: str) -> Path:
@@ -182,22 +183,32 @@ class Storage:
     def gpu_batches(self) -> int:
         return self._batcher.batches
 
+    def _publish_sync(self, tmp: str, object_id: str) -> None:
+        """Worker thread: give the spooled file its content-derived name (or drop it if that
+        content is already stored) and, with refcount=True, count one more holder."""
+        target = os.path.join(str(self.storage_path), object_id)
+        present = os.path.exists(target)
+        if present:
+            if os.path.exists(tmp):
+                os.unlink(tmp)  # same content already stored
+        else:
+            os.rename(tmp, target)  # atomic within the store directory
+        if self._refcount:
+            refs = os.path.join(str(self.storage_path), f".refs-{object_id}")
+            try:
+                holders = int(open(refs).read().strip() or 0)
+            except (FileNotFoundError, ValueError):
+                holders = 1 if present else 0
+            with open(refs, "w") as f:
+                f.write(str(holders + 1))
+
     async def _publish(self, tmp: Path, object_id: str) -> None:
-        target = self.storage_path / object_id
+        loop = asyncio.get_running_loop()
         if self._refcount:
             async with self._lock_refs():
-                holders = await self._read_refs(object_id) if await target.exists() else 0
-                await self._publish_file(tmp, target)
-                await self._refs_path(object_id).write_text(str(holders + 1))
+                await loop.run_in_executor(None, self._publish_sync, str(tmp), object_id)
         else:
-            await self._publish_file(tmp, target)
-
-    @staticmethod
-    async def _publish_file(tmp: Path, target: Path) -> None:
-        if await target.exists():
-            await tmp.unlink(missing_ok=True)  # same content already stored
-        else:
-            await tmp.rename(target)  # atomic within the store directory
+            await loop.run_in_executor(None, self._publish_sync, str(tmp), object_id)
 
     @asynccontextmanager
     async def writer(self) -> AsyncIterator[ObjectWriter]:
@@ -207,9 +218,15 @@ class Storage:
         The final hash can be retrieved by using the `.hash` attribute once the
         context has been left (the id depends on every byte written).
         """
-        await self.storage_path.mkdir(parents=True, exist_ok=True)
+        if not self._dir_ready:  # one hop, the first time only
+            await self.storage_path.mkdir(parents=True, exist_ok=True)
+            self._dir_ready = True
         tmp = self.storage_path / f".tmp-{secrets.token_hex(16)}"
-        file = await tmp.open("wb")
+        try:
+            file = await tmp.open("wb")
+        except FileNotFoundError:  # the directory went away since the first writer: make it again
+            await self.storage_path.mkdir(parents=True, exist_ok=True)
+            file = await tmp.open("wb")
         from_file = self._batcher.reads_files  # the engine preads the spooled file: O(1) memory per writer
         spool = _SpoolWriter(file, keep_chunks=not from_file)
         try:
