@@ -113,6 +113,6 @@ def bind_to_gpu_numa_node(local_rank: int) -> dict:
         if allowed:
             os.sched_setaffinity(0, allowed)
             info["cpus"] = len(allowed)
-    except (OSError, ValueError, AttributeError):
+    except Exception:  # noqa: BLE001 - topology is a hint; any failure means "leave the process alone"
         pass
     return info
