@@ -858,9 +858,8 @@ int cas_hash_files(cas_ctx* ctx, const char* const* paths, uint64_t n, void* out
 // cas_hash_host stages each wave in device buffers it gets from cudaMalloc and in
 // pinned memory from cudaHostAlloc.  Some callers cannot afford that: a request
 // handler on a latency budget (cudaMalloc synchronises the whole device and can
-// stall every other stream), a process whose device memory is already handed out
-// to another allocator or capped by its operator, or code that is inside a region
-// where the runtime forbids allocation.  For them the device staging lives in the
+// stall every other stream), or a process whose device memory is already handed out
+// to another allocator or capped by its operator.  For them the device staging lives in the
 // file-scope array below: fixed size, part of the loaded module, held by every GPU
 // that loads this library until the process exits.
 //

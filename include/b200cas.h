@@ -131,9 +131,8 @@ int cas_int32_peak(cas_ctx* ctx, int mode, int steps, double* lane_ops_per_s, do
  *
  * cas_hash_host gets its device and pinned staging from cudaMalloc/cudaHostAlloc.  A caller
  * that cannot allocate -- a request handler that must not take cudaMalloc's device-wide
- * synchronisation, a process whose GPU memory is fully owned by another allocator or capped
- * by its operator, code running where the runtime forbids allocation -- uses this entry
- * point instead: the device staging is a fixed array inside the library
+ * synchronisation, or a process whose GPU memory is fully owned by another allocator or
+ * capped by its operator -- uses this entry point instead: the device staging is a fixed array inside the library
  * (CAS_STATIC_MAX_BYTES + 48 bytes per object slot, about 8.05 MiB), resident on every GPU
  * that loads the library until the process exits.  No context is needed.
  *
