@@ -42,7 +42,7 @@ namespace {
 
 constexpr uint64_t MiB = 1ull << 20;
 
-std::string g_create_error;
+thread_local std::string g_create_error;  // errors that have no context (cas_create, cas_hash_host_static), per calling thread
 
 // Small fork-join pool for packing objects into pinned staging.
 class PackPool {

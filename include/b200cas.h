@@ -58,7 +58,8 @@ typedef struct cas_ctx cas_ctx;
  * `Storage(storage_path)` instance would own (storage.py:41-42). */
 int cas_create(int device, cas_ctx** out);
 void cas_destroy(cas_ctx* ctx);
-/* Last error text of `ctx`, or of the last failed cas_create when ctx is NULL. */
+/* Last error text of `ctx`; with ctx == NULL, of the calling thread's last failed call that had no
+ * context (cas_create, cas_hash_host_static). */
 const char* cas_last_error(const cas_ctx* ctx);
 int cas_set_option(cas_ctx* ctx, int key, int64_t value);
 int cas_get_option(const cas_ctx* ctx, int key, int64_t* value);
