@@ -101,6 +101,34 @@ def test_http_round_trip_on_the_gpu_store(tmp_path, hasher):
         assert got.content == b"x" * 3000
 
 
+def test_two_contexts_on_one_device_from_two_threads():
+    """Contexts are independent (own streams, arena, staging): two host threads may hash at once."""
+    import threading
+
+    from bee_code_interpreter_fs_b200 import GpuHasher
+
+    blobs = [[os.urandom(1000 + 37 * i) for i in range(400)] + [os.urandom(3 << 20)] for _ in range(2)]
+    want = [[hashlib.sha256(b).hexdigest() for b in bl] for bl in blobs]
+    got = [None, None]
+    errors = []
+
+    def run(k):
+        try:
+            with GpuHasher(0) as h:
+                for _ in range(5):
+                    got[k] = h.hash_many(blobs[k])
+        except Exception as e:  # noqa: BLE001
+            errors.append(e)
+
+    threads = [threading.Thread(target=run, args=(k,)) for k in range(2)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errors, errors
+    assert got == want
+
+
 def test_multi_gpu_hasher_on_visible_devices():
     mh = MultiGpuHasher()
     blobs = [os.urandom(n) for n in (0, 5, 64, 100000, 3, 70000, 1 << 20)] * 3
