@@ -141,6 +141,7 @@ struct cas_ctx {
     uint64_t obj_cap = 0;
     PackPool* pool = nullptr;
     uint32_t* d_sink = nullptr;
+    bool host_path_dirty = false;  // set while a host-path call is in progress; stays set if it failed
 };
 
 namespace {
@@ -643,6 +644,10 @@ int hash_host_impl(cas_ctx* ctx, const ByteSource& srcs, const uint64_t* len, ui
     const uint8_t* hbase = srcs.hbase;
     const uint64_t* off = srcs.off;
     const bool from_files = srcs.paths != nullptr;
+    // A call that failed half-way may have left copies and kernels in flight on buffers
+    // this call is about to reuse: wait them out before touching anything.
+    if (ctx->host_path_dirty) CU(cudaDeviceSynchronize());
+    ctx->host_path_dirty = true;
 
     // Schedule: longest first when lengths differ, so that the 32 lanes of a warp
     // carry messages of (nearly) equal block counts and the long chains start early.
@@ -810,6 +815,7 @@ int hash_host_impl(cas_ctx* ctx, const ByteSource& srcs, const uint64_t* len, ui
     } else {
         for (uint64_t k = 0; k < n; ++k) memcpy(out + 32ull * order[k], ctx->h_dig + 32ull * k, 32);
     }
+    ctx->host_path_dirty = false;
     return CAS_OK;
 }
 
