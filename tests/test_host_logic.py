@@ -185,6 +185,47 @@ def test_streaming_writers_are_hashed_from_their_spool_files(tmp_path, oracle_fi
     assert sorted(os.listdir(tmp_path)) == sorted(ids[:8])
 
 
+def test_group_commit_batches_and_per_request_errors(tmp_path, oracle_hasher):
+    """A lone writer is not delayed; writers that queue behind a running batch go out together;
+    max_batch caps a batch; a failure while storing one object reaches that caller only."""
+    import time
+
+    class SlowHasher:
+        def __init__(self):
+            self.sizes = []
+
+        def hash_many(self, objs):
+            self.sizes.append(len(objs))
+            time.sleep(0.05)
+            return [hashlib.sha256(o).hexdigest() for o in objs]
+
+    async def go():
+        slow = SlowHasher()
+        st = Storage(str(tmp_path / "a"), hasher=slow, max_batch=8)
+        t0 = time.perf_counter()
+        await st.write(b"alone")
+        assert time.perf_counter() - t0 < 0.5 and slow.sizes == [1]
+        ids = await asyncio.gather(*(st.write(b"obj-%d" % i) for i in range(20)))
+        assert ids == [hashlib.sha256(b"obj-%d" % i).hexdigest() for i in range(20)]
+        assert sum(slow.sizes) == 21 and max(slow.sizes) <= 8 and len(slow.sizes) <= 6
+
+        st2 = Storage(str(tmp_path / "b"), hasher=oracle_hasher)
+        real = st2._store_sync
+
+        def flaky(data, object_id):
+            if data == b"bad":
+                raise OSError("disk full")
+            real(data, object_id)
+
+        st2._store_sync = flaky
+        results = await asyncio.gather(st2._batcher.hash(b"ok", lambda i: flaky(b"ok", i)),
+                                       st2._batcher.hash(b"bad", lambda i: flaky(b"bad", i)), return_exceptions=True)
+        assert results[0] == hashlib.sha256(b"ok").hexdigest() and isinstance(results[1], OSError)
+        assert await st2.exists(results[0])
+
+    run(go())
+
+
 def test_write_many_and_verify(tmp_path, oracle_hasher):
     async def go():
         st = Storage(str(tmp_path), hasher=oracle_hasher)
