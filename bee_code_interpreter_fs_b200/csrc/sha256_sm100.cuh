@@ -39,7 +39,9 @@ __device__ __forceinline__ uint32_t lop_maj(uint32_t a, uint32_t b, uint32_t c) 
     asm("lop3.b32 %0, %1, %2, %3, 0xE8;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
     return d;
 }
-// a + b on the FMA pipe: a * one + b with one == 1 at run time.
+// a + b on the FMA pipe: a * one + b with one == 1 at run time.  (With a literal 1 ptxas folds the
+// multiply away and merges the adds back into IADD3 on the ALU pipe; with the 1 in constant memory or
+// without inline asm it still keeps the multiplier in a vector register -- both tried, same SASS.)
 __device__ __forceinline__ uint32_t fma_add(uint32_t a, uint32_t b, uint32_t one) {
     uint32_t d;
     asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(one), "r"(b));
