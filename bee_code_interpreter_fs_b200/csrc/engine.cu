@@ -125,7 +125,7 @@ struct cas_ctx {
     int pack_threads = 0;
     uint64_t launches = 0;
     uint64_t arena_max = 32ull << 30;  // device bytes the host path may hold (two halves)
-    uint64_t long_max_objects = 1536;  // batches up to this many objects may go one warp per object
+    uint64_t long_max_objects = 592;   // batches up to this many objects may go one warp per object (set to 4 x SMs)
     uint64_t long_min_bytes = 32768;   // ... if the objects are at least this long
     cudaStream_t s_copy = nullptr;
     cudaStream_t s_comp[NCOMP] = {};
@@ -409,6 +409,9 @@ int cas_create(int device, cas_ctx** out) {
     cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, device);
     ctx->clock_khz = khz;
     ctx->mem_bytes = prop.totalGlobalMem;
+    // One warp per SM sub-partition is where the warp-per-object kernel keeps its full per-chain speed;
+    // beyond that, lanes (spread one warp per CTA) are faster again.
+    ctx->long_max_objects = 4ull * (uint64_t)prop.multiProcessorCount;
     cudaDriverEntryPointQueryResult qres;
     e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ctx->encode_tiled, cudaEnableDefault, &qres);
     if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !ctx->encode_tiled) {

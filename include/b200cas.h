@@ -50,7 +50,7 @@ typedef struct cas_ctx cas_ctx;
 
 #define CAS_OPT_ARENA_BYTES 6   /* host path: most device memory the staging arena may take (default 32 GiB) */
 
-#define CAS_OPT_LONG_MAX_OBJECTS 7 /* batches of at most this many objects may run one warp per object (default 1536; 0 = never) */
+#define CAS_OPT_LONG_MAX_OBJECTS 7 /* batches of at most this many objects may run one warp per object (default 4 x SM count = 592; 0 = never) */
 #define CAS_OPT_LONG_MIN_BYTES 8   /* ... when the objects are at least this long (default 32 KiB) */
 
 /* Create / destroy the per-device context (streams, staging buffers are made
@@ -105,7 +105,7 @@ int cas_hash_device(cas_ctx* ctx, const void* d_base, const uint64_t* d_off, con
  * Same contract as cas_hash_device, but one WARP per object instead of one lane: the
  * message schedule of 32 blocks is expanded in parallel by the warp's lanes and only the
  * 64 rounds stay on the serial chain.  About 3x faster per object; use it when the batch
- * has so few objects (up to ~1.5 k) that lanes would leave the GPU empty -- BASELINE.json
+ * has so few objects (up to one per SM sub-partition, 592) that lanes would leave the GPU empty -- BASELINE.json
  * config 5 (64 x 1 GiB), a single large upload.  Digests are identical.
  */
 int cas_hash_device_long(cas_ctx* ctx, const void* d_base, const uint64_t* d_off, const uint64_t* d_len,

@@ -144,11 +144,13 @@ def test_few_long_uniform_objects_take_the_warp_kernel_and_agree_with_lanes(hash
     buf = torch.empty(n * stride, dtype=torch.uint8, device="cuda:0")
     hasher.gen_synthetic(buf, 123, 0, n, length, stride)
     a = hexes(hasher.digest_device_uniform(buf, stride, length, n).cpu().numpy())  # warp per object (n small)
+    saved = hasher.get_option(_ffi.OPT_LONG_MAX_OBJECTS)
+    assert saved == 4 * hasher.device_info()["sm_count"]
     hasher.set_option(_ffi.OPT_LONG_MAX_OBJECTS, 0)
     try:
         b = hexes(hasher.digest_device_uniform(buf, stride, length, n).cpu().numpy())  # lane per object
     finally:
-        hasher.set_option(_ffi.OPT_LONG_MAX_OBJECTS, 1536)
+        hasher.set_option(_ffi.OPT_LONG_MAX_OBJECTS, saved)
     assert a == b
     assert a[0] == hashlib.sha256(oracle.synth_object(123, 0, length)).hexdigest()
     assert a[-1] == hashlib.sha256(oracle.synth_object(123, n - 1, length)).hexdigest()

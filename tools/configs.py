@@ -188,7 +188,7 @@ def c5(h):
     out = torch.empty((n, 32), dtype=torch.uint8, device="cuda:0")
     res = {"objects": n, "object_bytes": length}
     for kernel, name in ((2, "warp_per_object"), (0, "lane_per_object")):
-        h.set_option(_ffi.OPT_LONG_MAX_OBJECTS, 1536 if kernel == 2 else 0)
+        h.set_option(_ffi.OPT_LONG_MAX_OBJECTS, 592 if kernel == 2 else 0)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         h.digest_device_uniform(buf, length, length, n, out=out)
@@ -198,7 +198,7 @@ def c5(h):
         res[f"kernel_ms_{name}"] = ms
         res[f"kernel_gb_s_{name}"] = n * length / ms / 1e6
         res[f"per_chain_gb_s_{name}"] = length / ms / 1e6
-    h.set_option(_ffi.OPT_LONG_MAX_OBJECTS, 1536)
+    h.set_option(_ffi.OPT_LONG_MAX_OBJECTS, 592)
     dig = out.cpu().numpy()
     first = buf[:length].cpu().numpy()
     t0 = time.perf_counter()
