@@ -18,13 +18,16 @@ def variants():
     v = []
     for c in (2, 3, 4):  # register budget through __launch_bounds__(256, c)
         v.append((f"lb_c{c}", dict(KB_MINCTAS=c)))
-    for cap in (64, 72, 80, 88, 96, 104, 112, 128, 168):  # ... and through __maxnreg__
+    for cap in (64, 72, 80, 96, 128):  # ... and through __maxnreg__
         v.append((f"cap{cap}", dict(KB_REGCAP=cap)))
         v.append((f"cap{cap}_t128", dict(KB_REGCAP=cap, KB_THREADS=128)))
     for cap in (80, 96):
         v.append((f"cap{cap}_s1", dict(KB_REGCAP=cap, KB_SCHED=1)))
         v.append((f"cap{cap}_fma2", dict(KB_REGCAP=cap, KB_FMA=2)))
         v.append((f"cap{cap}_n3", dict(KB_REGCAP=cap, KB_NSTAGE=3)))
+    for threads, cap in ((160, 80), (192, 80), (224, 72), (384, 80), (512, 64)):  # other warp counts per SM
+        v.append((f"t{threads}_cap{cap}", dict(KB_REGCAP=cap, KB_THREADS=threads)))
+    v.append(("m2_c2", dict(KB_MSGS=2, KB_MINCTAS=2)))  # two messages per lane
     return v
 
 
