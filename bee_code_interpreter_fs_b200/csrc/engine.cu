@@ -902,6 +902,8 @@ int cas_hash_host_static(int device, const void* base, const uint64_t* off, cons
     uint64_t slot[CAS_STATIC_MAX_OBJECTS], length[CAS_STATIC_MAX_OBJECTS];
     uint64_t cursor = 0;
     for (uint64_t i = 0; i < n; ++i) {
+        if (len[i] && !base && !off[i])
+            return static_fail(CAS_E_ARG, "cas_hash_host_static: a non-empty object has a NULL address");
         if (len[i] > CAS_STATIC_MAX_BYTES || cursor + align16(len[i]) > CAS_STATIC_MAX_BYTES) {
             char msg[200];
             snprintf(msg, sizeof msg,
@@ -915,8 +917,15 @@ int cas_hash_host_static(int device, const void* base, const uint64_t* off, cons
         cursor += align16(len[i]);
     }
     std::lock_guard<std::mutex> lock(g_static_mutex);
+    // The calling thread gets its current device back on every return path.
+    struct DeviceGuard {
+        int prev = -1;
+        ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+    } guard;
+    if (cudaGetDevice(&guard.prev) != cudaSuccess) { cudaGetLastError(); guard.prev = -1; }
     cudaError_t e = cudaSetDevice(device);
     if (e != cudaSuccess) return static_fail(CAS_E_CUDA, "cas_hash_host_static: cudaSetDevice", e);
+    if (guard.prev == device) guard.prev = -1;  // nothing to restore
     if (!g_static_ptr[device]) {
         // Once per device, with that device current.
         void* p = nullptr;
@@ -931,19 +940,29 @@ int cas_hash_host_static(int device, const void* base, const uint64_t* off, cons
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const uint8_t* hbase = static_cast<const uint8_t*>(base);
 
+    // Once something is queued on the stream, a failure must not hand the shared array to
+    // the next caller while this call's copies or kernel may still be running on it: every
+    // error return below waits for the stream first (the result of that wait is not the
+    // error being reported, so it is ignored).
+    auto fail_drained = [&](const char* what, cudaError_t err) {
+        cudaStreamSynchronize(st);
+        cudaGetLastError();
+        return static_fail(CAS_E_CUDA, what, err);
+    };
+
     // The array keeps whatever the previous call left.  Object bytes, offsets and
     // lengths are all rewritten below before the kernel reads them; the digest
     // slots are the one thing that must not carry over, so they start at zero.
     e = cudaMemsetAsync(d_dig, 0, n * 32, st);
-    if (e != cudaSuccess) return static_fail(CAS_E_CUDA, "cas_hash_host_static: cudaMemsetAsync", e);
+    if (e != cudaSuccess) return fail_drained("cas_hash_host_static: cudaMemsetAsync", e);
     for (uint64_t i = 0; i < n; ++i) {
         if (!length[i]) continue;
         e = cudaMemcpyAsync(d_data + slot[i], hbase + off[i], length[i], cudaMemcpyHostToDevice, st);
-        if (e != cudaSuccess) return static_fail(CAS_E_CUDA, "cas_hash_host_static: copy of an object to the device", e);
+        if (e != cudaSuccess) return fail_drained("cas_hash_host_static: copy of an object to the device", e);
     }
     e = cudaMemcpyAsync(d_off, slot, n * 8, cudaMemcpyHostToDevice, st);
     if (e == cudaSuccess) e = cudaMemcpyAsync(d_len, length, n * 8, cudaMemcpyHostToDevice, st);
-    if (e != cudaSuccess) return static_fail(CAS_E_CUDA, "cas_hash_host_static: copy of offsets/lengths", e);
+    if (e != cudaSuccess) return fail_drained("cas_hash_host_static: copy of offsets/lengths", e);
     cas::BatchArgs a{};
     a.base = d_data;
     a.off = d_off;
@@ -954,10 +973,11 @@ int cas_hash_host_static(int device, const void* base, const uint64_t* off, cons
     a.zero = 0u;
     cas::kernel_ldg<3, THREADS, 4><<<(unsigned)((n + THREADS - 1) / THREADS), THREADS, 0, st>>>(a);
     e = cudaGetLastError();
-    if (e != cudaSuccess) return static_fail(CAS_E_CUDA, "cas_hash_host_static: kernel launch", e);
+    if (e != cudaSuccess) return fail_drained("cas_hash_host_static: kernel launch", e);
     e = cudaMemcpyAsync(out32n, d_dig, n * 32, cudaMemcpyDeviceToHost, st);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
-    if (e != cudaSuccess) return static_fail(CAS_E_CUDA, "cas_hash_host_static: digest copy / synchronize", e);
+    if (e != cudaSuccess) return fail_drained("cas_hash_host_static: digest copy", e);
+    e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) return static_fail(CAS_E_CUDA, "cas_hash_host_static: synchronize", e);
     return CAS_OK;
 }
 

@@ -406,6 +406,10 @@ __device__ __forceinline__ void tma_body(const TensorMapBlob& tmap, const BatchA
             }
         }
         sha256_compress_multi<FMA_LEVEL, MSGS, SCHED>(st, w, one);
+        // Every lane's LDS reads of this stage must have completed before the async proxy may
+        // overwrite it: the warp reconverges here explicitly (independent thread scheduling
+        // gives no such guarantee after the divergent try_wait spin above).
+        __syncwarp();
         if (lane == 0 && i + NSTAGE < nb) {
             uint32_t bytes;
             asm volatile("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(bytes) : "r"(st[0][0] | st[MSGS - 1][0]), "r"(A.zero), "r"(STAGE));

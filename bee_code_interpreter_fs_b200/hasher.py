@@ -241,11 +241,33 @@ class MultiGpuHasher:
         for h in self.hashers:
             h.close()
 
+    def digest_packed(self, base, off, length) -> np.ndarray:
+        """Digests of ``base[off[i]:off[i]+length[i]]`` (host memory), sharded by object."""
+        off = np.ascontiguousarray(off, dtype=np.uint64)
+        length = np.ascontiguousarray(length, dtype=np.uint64)
+        if base is None:
+            bptr = 0
+        elif isinstance(base, np.ndarray):
+            bptr = base.ctypes.data
+        elif hasattr(base, "data_ptr"):
+            bptr = base.data_ptr()
+        else:
+            bptr = int(base)
+        return self._digest_addresses(off + np.uint64(bptr), length)
+
     def digest_many(self, objs: Sequence[BytesLike]) -> np.ndarray:
         n = len(objs)
         if n == 0:
             return np.empty((0, 32), dtype=np.uint8)
         addr, length, keep = _addresses(objs)
+        out = self._digest_addresses(addr, length)
+        del keep
+        return out
+
+    def _digest_addresses(self, addr: np.ndarray, length: np.ndarray) -> np.ndarray:
+        n = int(addr.shape[0])
+        if n == 0:
+            return np.empty((0, 32), dtype=np.uint8)
         parts = shard.assign(length, len(self.hashers))
         results: list = [None] * len(self.hashers)
         errors: list = []
@@ -262,7 +284,6 @@ class MultiGpuHasher:
             t.start()
         for t in threads:
             t.join()
-        del keep
         if errors:
             raise errors[0]
         return shard.scatter_back(parts, results, n)

@@ -19,6 +19,8 @@
  * 32 raw bytes of SHA-256 (FIPS 180-4), bit-exact with hashlib.sha256; hex
  * encoding (the 64-character id of storage.py:52's shape) is done by the caller.
  * There is no CPU fallback: without a usable CUDA device every call fails.
+ * Calls that take a context make that context's device the calling thread's current
+ * CUDA device and leave it so (cudaSetDevice); cas_hash_host_static restores the caller's.
  */
 #ifndef B200CAS_H
 #define B200CAS_H
@@ -151,6 +153,12 @@ int cas_int32_peak(cas_ctx* ctx, int mode, int steps, double* lane_ops_per_s, do
  * is rewritten first and the digest slots are zeroed first.  Calls are serialised by a
  * lock inside the library, because two calls in flight on the same GPU would overwrite
  * each other's staging and race.
+ *
+ * `stream` must be a stream of `device` (or NULL).  The calling thread's current device is
+ * the same after the call as before it.  If a copy or the launch fails part-way, the call
+ * waits for whatever it had already queued on `stream` before it returns the error, so a
+ * failed call never leaves work running on the array the next caller is about to reuse.
+ * A non-empty object with a NULL address (base == NULL and off[i] == 0) is rejected.
  */
 #define CAS_STATIC_MAX_OBJECTS 1024
 #define CAS_STATIC_MAX_BYTES (8u << 20)

@@ -213,16 +213,15 @@ def test_host_path_pinned_contiguous_and_mixed_types(hasher):
 
 
 def test_million_a_and_half_gib_message_use_64bit_length(hasher, kat):
+    """The FIPS one-million-'a' vector, and a message just over 2^29 bytes (its bit length needs
+    33 bits) through the warp-per-object kernel.  tests/test_gpu_configs.py sends a 2^30-byte
+    object through the lane kernels as well."""
     assert hasher.hash_one(b"a" * 1_000_000) == kat["fips"][4]["sha256"]
-    n = (1 << 29) + 5  # bit length needs more than 32 bits
-    for kernel in (0, 2):
-        configure(hasher, kernel)
-        buf = torch.empty(n + 11, dtype=torch.uint8, device="cuda:0")
-        hasher.gen_synthetic(buf, 77, 3, 1, n, n)
-        got = hexes(hasher.digest_device_uniform(buf, n + 11 if kernel == 0 else n + 11, n, 1).cpu().numpy())[0]
-        want = hashlib.sha256(buf[:n].cpu().numpy().tobytes()).hexdigest()
-        assert got == want
-        del buf
+    n = (1 << 29) + 5
+    buf = torch.empty(n + 11, dtype=torch.uint8, device="cuda:0")
+    hasher.gen_synthetic(buf, 77, 3, 1, n, n)
+    got = hexes(hasher.digest_device_uniform(buf, n + 11, n, 1).cpu().numpy())[0]
+    assert got == hashlib.sha256(buf[:n].cpu().numpy().tobytes()).hexdigest()
 
 
 # ------------------------------------------ full-size, size-independent properties --

@@ -4,12 +4,14 @@ Some users of this library must not let it call cudaMalloc/cudaHostAlloc for the
 request handler that cannot take cudaMalloc's device-wide synchronisation, a process whose
 GPU memory is already owned by another allocator or capped by its operator.  This test
 calls the entry point through the C ABI and checks it, bit for bit, against the regular
-host path (cas_hash_host) on the same objects, twice in a row: the second call finds the
-first call's bytes still in the shared scratch array and must not be affected by them.
+host path (cas_hash_host) and against hashlib.sha256 on the same objects, twice in a row:
+the second call finds the first call's bytes still in the shared scratch array and must not
+be affected by them.
 Collected last on purpose (file name), and self-contained so that it also passes alone in
 a fresh process.
 """
 import ctypes
+import hashlib
 
 import numpy as np
 import pytest
@@ -38,6 +40,10 @@ def _static_digests(lib, objs, device=0):
     return rc, out
 
 
+def _hashlib_digests(objs):
+    return np.frombuffer(b"".join(hashlib.sha256(o).digest() for o in objs), dtype=np.uint8).reshape(-1, 32)
+
+
 def test_static_entry_point_matches_regular_host_path_twice():
     lib = _ffi.load()
     with GpuHasher(0) as h:
@@ -46,13 +52,15 @@ def test_static_entry_point_matches_regular_host_path_twice():
         rc, got = _static_digests(lib, first)
         assert rc == _ffi.CAS_OK, lib.cas_last_error(None)
         assert (got == h.digest_many(first)).all()
+        assert (got == _hashlib_digests(first)).all()
         # second call, straight after: fewer, shorter, different objects over the stale bytes
         second = _batch(2, 300, 3000)
         rc, got = _static_digests(lib, second)
         assert rc == _ffi.CAS_OK, lib.cas_last_error(None)
         assert (got == h.digest_many(second)).all()
+        assert (got == _hashlib_digests(second)).all()
         # and the Python helper gives the same ids as the regular path
-        assert hash_many_static(second) == h.hash_many(second)
+        assert hash_many_static(second) == h.hash_many(second) == [hashlib.sha256(o).hexdigest() for o in second]
 
 
 def test_static_entry_point_rejects_what_does_not_fit():
@@ -69,3 +77,37 @@ def test_static_entry_point_rejects_what_does_not_fit():
     assert rc == _ffi.CAS_OK, lib.cas_last_error(None)
     with GpuHasher(0) as h:
         assert (got == h.digest_many(edge)).all()
+    assert (got == _hashlib_digests(edge)).all()
+
+
+def test_static_entry_point_recovers_after_a_call_that_failed_half_way():
+    """A call that fails after it has queued work must wait that work out before it gives the
+    shared array up, and must leave the calling thread's device alone.  Here the output pointer
+    is device memory, which the final device-to-host copy refuses -- after the object copies and
+    the kernel are already on the stream.  The next call has to succeed and be exact."""
+    import torch
+
+    lib = _ffi.load()
+    objs = _batch(3, 500, 6000)
+    n = len(objs)
+    ptrs = (ctypes.c_char_p * n)(*objs)
+    off = np.frombuffer(ptrs, dtype=np.uint64, count=n).copy()
+    length = np.fromiter(map(len, objs), dtype=np.uint64, count=n)
+    bad_out = torch.zeros(n * 32, dtype=torch.uint8, device="cuda:0")
+    torch.cuda.synchronize()
+    before = torch.cuda.current_device()
+    rc = lib.cas_hash_host_static(0, None, off.ctypes.data, length.ctypes.data, n, bad_out.data_ptr(), None)
+    assert rc == _ffi.CAS_E_CUDA and b"digest copy" in lib.cas_last_error(None)
+    assert torch.cuda.current_device() == before
+    rc = lib.cas_hash_host_static(0, None, None, length.ctypes.data, n, bad_out.data_ptr(), None)
+    assert rc == _ffi.CAS_E_ARG
+    null_src = np.zeros(1, dtype=np.uint64)
+    one_len = np.ones(1, dtype=np.uint64)
+    out = np.zeros((1, 32), dtype=np.uint8)
+    rc = lib.cas_hash_host_static(0, None, null_src.ctypes.data, one_len.ctypes.data, 1, out.ctypes.data, None)
+    assert rc == _ffi.CAS_E_ARG and b"NULL address" in lib.cas_last_error(None)
+    # straight after the failures: a different batch over the stale bytes, exact
+    again = _batch(4, 400, 5000)
+    rc, got = _static_digests(lib, again)
+    assert rc == _ffi.CAS_OK, lib.cas_last_error(None)
+    assert (got == _hashlib_digests(again)).all()

@@ -16,6 +16,15 @@
 #ifndef KB_FMA
 #define KB_FMA 3
 #endif
+#ifndef KB_M
+#define KB_M 1
+#endif
+#ifndef KB_ACT
+#define KB_ACT 32
+#endif
+#ifndef KB_ROTF
+#define KB_ROTF 0
+#endif
 #ifndef KB_NAME
 #define KB_NAME "long"
 #endif
@@ -40,7 +49,7 @@ static uint64_t checksum(const uint8_t* d_out, uint64_t n) {
 int main(int argc, char** argv) {
     const uint64_t L = argc > 1 ? strtoull(argv[1], 0, 10) : (16ull << 20) + 5;
     uint8_t *buf, *out;
-    const uint64_t nmax = 2368;
+    const uint64_t nmax = argc > 2 ? strtoull(argv[2], 0, 10) : 2368;
     const uint64_t stride = (L + 15) & ~15ull;
     CK(cudaMalloc(&buf, nmax * stride));
     CK(cudaMalloc(&out, nmax * 32));
@@ -50,14 +59,20 @@ int main(int argc, char** argv) {
     cudaEvent_t e0, e1;
     CK(cudaEventCreate(&e0));
     CK(cudaEventCreate(&e1));
-    const uint64_t counts[] = {1, 64, 148, 592, 1184, 2368};
+    std::vector<uint64_t> counts;
+    if (argc > 3) {
+        for (int i = 3; i < argc; ++i) counts.push_back(strtoull(argv[i], 0, 10));
+    } else {
+        counts = {1, 64, 148, 592, 1184, 2368};
+    }
     for (uint64_t n : counts) {
+        if (n > nmax) continue;
         cas::BatchArgs a{};
         a.base = buf; a.stride = stride; a.ulen = L; a.n = n; a.out = out; a.one = 1; a.zero = 0;
         float ms_long = 0, ms_lane = 0;
         CK(cudaMemset(out, 0, n * 32));
         CK(cudaEventRecord(e0));
-        cas::kernel_long<KB_FMA, KB_ADDS><<<(unsigned)n, 32, cas::LONG_SMEM_PER_WARP>>>(a);
+        cas::kernel_long<KB_FMA, KB_ADDS, KB_M, KB_ACT, KB_ROTF><<<(unsigned)((n + KB_M - 1) / KB_M), 32, cas::LONG_SMEM_PER_WARP>>>(a);
         CK(cudaGetLastError());
         CK(cudaEventRecord(e1));
         CK(cudaEventSynchronize(e1));
@@ -65,7 +80,7 @@ int main(int argc, char** argv) {
         const uint64_t c_long = checksum(out, n);
         CK(cudaMemset(out, 0, n * 32));
         CK(cudaEventRecord(e0));
-        cas::kernel_ldg<3, 256, 4><<<(unsigned)((n + 255) / 256), 256>>>(a);
+        cas::kernel_ldg<3, 32, 16><<<(unsigned)((n + 31) / 32), 32>>>(a);  // one warp per CTA, as the engine launches small batches
         CK(cudaGetLastError());
         CK(cudaEventRecord(e1));
         CK(cudaEventSynchronize(e1));
