@@ -10,12 +10,14 @@ CAS_OK = 0
 CAS_E_CUDA, CAS_E_ARG, CAS_E_NOMEM, CAS_E_NODEVICE, CAS_E_IO = -1, -2, -3, -4, -5
 OPT_KERNEL, OPT_FMA_LEVEL, OPT_WAVE_BYTES, OPT_PACK_THREADS, OPT_CTAS_PER_SM, OPT_ARENA_BYTES = 1, 2, 3, 4, 5, 6
 OPT_LONG_MAX_OBJECTS, OPT_LONG_MIN_BYTES = 7, 8
+OPT_LONG_MAX_PER_WARP, OPT_FIRST_CHUNK_BYTES, OPT_IO_THREADS = 9, 10, 11
+STORED_NEW, STORED_EXISTED = 0, 1
 
 # Every symbol include/b200cas.h declares (tests check the library exports them all).
 SYMBOLS = (
     "cas_create", "cas_destroy", "cas_last_error", "cas_set_option", "cas_get_option", "cas_device_info",
     "cas_hash_host", "cas_hash_files", "cas_hash_device", "cas_hash_device_long", "cas_hash_device_uniform", "cas_gen_synthetic", "cas_int32_peak",
-    "cas_launch_count", "cas_version", "cas_hash_host_static",
+    "cas_launch_count", "cas_version", "cas_hash_host_static", "cas_reserve", "cas_store_host", "cas_publish_files",
 )
 STATIC_MAX_OBJECTS = 1024
 STATIC_MAX_BYTES = 8 << 20
@@ -71,6 +73,12 @@ def load() -> ctypes.CDLL:
     lib.cas_int32_peak.restype = ci
     lib.cas_hash_host_static.argtypes = [ci, vp, vp, vp, u64, vp, vp]
     lib.cas_hash_host_static.restype = ci
+    lib.cas_reserve.argtypes = [vp, u64, u64]
+    lib.cas_reserve.restype = ci
+    lib.cas_store_host.argtypes = [vp, ctypes.c_char_p, vp, vp, vp, u64, vp, vp]
+    lib.cas_store_host.restype = ci
+    lib.cas_publish_files.argtypes = [vp, ctypes.c_char_p, vp, u64, vp, vp, vp]
+    lib.cas_publish_files.restype = ci
     lib.cas_launch_count.argtypes = [vp]
     lib.cas_launch_count.restype = u64
     lib.cas_version.argtypes = []

@@ -17,12 +17,15 @@
 #include <errno.h>
 #include <fcntl.h>
 #include <sys/stat.h>
+#include <sys/syscall.h>
+#include <sys/time.h>
 #include <unistd.h>
 #include <stdint.h>
 #include <stdio.h>
 #include <string.h>
 
 #include <algorithm>
+#include <chrono>
 #include <atomic>
 #include <condition_variable>
 #include <functional>
@@ -62,11 +65,19 @@ public:
     int size() const { return (int)th_.size(); }
     // Runs fn(worker_index) on every worker and waits for all of them.
     void run(const std::function<void(int)>& fn) {
-        std::unique_lock<std::mutex> lk(m_);
+        start(fn);
+        wait();
+    }
+    // The same in two halves, so that the caller can work meanwhile.  `fn` must stay alive until wait() returns.
+    void start(const std::function<void(int)>& fn) {
+        std::lock_guard<std::mutex> lk(m_);
         fn_ = &fn;
         pending_ = (int)th_.size();
         ++gen_;
         cv_.notify_all();
+    }
+    void wait() {
+        std::unique_lock<std::mutex> lk(m_);
         done_.wait(lk, [this] { return pending_ == 0; });
         fn_ = nullptr;
     }
@@ -127,6 +138,8 @@ struct cas_ctx {
     uint64_t arena_max = 32ull << 30;  // device bytes the host path may hold (two halves)
     uint64_t long_max_objects = 592;   // batches up to this many objects may go one warp per object (set to 4 x SMs)
     uint64_t long_min_bytes = 32768;   // ... if the objects are at least this long
+    int long_max_m = 32;               // groups of up to long_max_objects x this many long objects run M objects per warp
+    uint64_t first_chunk = 2 * MiB;    // host path: size of the first copy chunk (chunks double up to the cap)
     cudaStream_t s_copy = nullptr;
     cudaStream_t s_comp[NCOMP] = {};
     cudaEvent_t ev_epoch[2][NCOMP] = {};  // kernels of the epoch that last used an arena half
@@ -140,6 +153,9 @@ struct cas_ctx {
     uint8_t* d_dig = nullptr;
     uint64_t obj_cap = 0;
     PackPool* pool = nullptr;
+    PackPool* io_pool = nullptr;  // file writers of cas_store_host (they run while the pack pool feeds the GPU)
+    int io_threads = 0;
+    bool trace = false;           // B200CAS_TRACE=1: one line of host-pipeline timings per call on stderr
     uint32_t* d_sink = nullptr;
     bool host_path_dirty = false;  // set while a host-path call is in progress; stays set if it failed
 };
@@ -263,17 +279,44 @@ int launch_batch(cas_ctx* ctx, cas::BatchArgs a, cudaStream_t st) {
     return CAS_OK;
 }
 
-// One warp per object (csrc/sha256_long.cuh): for few, long objects.
-int launch_long(cas_ctx* ctx, cas::BatchArgs a, cudaStream_t st) {
+// One warp per M objects (csrc/sha256_long.cuh): for few, long objects.
+template <int M>
+cudaError_t launch_long_m(const cas::BatchArgs& a, cudaStream_t st) {
+    cas::kernel_long<3, 4, M><<<(unsigned)((a.n + M - 1) / M), 32, cas::LONG_SMEM_PER_WARP, st>>>(a);
+    return cudaGetLastError();
+}
+
+int launch_long(cas_ctx* ctx, cas::BatchArgs a, cudaStream_t st, int m = 1) {
     if (a.n == 0) return CAS_OK;
     if (a.n > 0x7FFFFFFFull) return fail(ctx, CAS_E_ARG, "too many objects for the warp-per-object kernel");
     a.one = 1u;
     a.zero = 0u;
-    cas::kernel_long<3, 1><<<(unsigned)a.n, 32, cas::LONG_SMEM_PER_WARP, st>>>(a);
-    cudaError_t e = cudaGetLastError();
+    cudaError_t e;
+    switch (m) {
+        case 1: e = launch_long_m<1>(a, st); break;
+        case 2: e = launch_long_m<2>(a, st); break;
+        case 4: e = launch_long_m<4>(a, st); break;
+        case 8: e = launch_long_m<8>(a, st); break;
+        case 16: e = launch_long_m<16>(a, st); break;
+        case 32: e = launch_long_m<32>(a, st); break;
+        default: return fail(ctx, CAS_E_ARG, "objects per warp must be 1, 2, 4, 8, 16 or 32");
+    }
     if (e != cudaSuccess) return fail(ctx, CAS_E_CUDA, "sha256 warp-per-object kernel launch", e);
     ++ctx->launches;
     return CAS_OK;
+}
+
+// One group of objects whose bytes are on the device: pick the kernel.  `min_len` is the
+// shortest object of the group.  Groups small enough to leave SM sub-partitions idle and
+// made of objects long enough to amortise the cooperative schedule expansion run M objects
+// per warp (kernel_long<M>, csrc/sha256_long.cuh); everything else one object per lane.
+int launch_group(cas_ctx* ctx, const cas::BatchArgs& a, uint64_t min_len, cudaStream_t cs) {
+    if (ctx->long_max_objects && min_len >= ctx->long_min_bytes && a.n <= ctx->long_max_objects * (uint64_t)ctx->long_max_m) {
+        int m = 1;
+        while ((uint64_t)m * ctx->long_max_objects < a.n) m *= 2;
+        return launch_long(ctx, a, cs, m);
+    }
+    return launch_batch(ctx, a, cs);
 }
 
 inline uint64_t align16(uint64_t x) { return (x + 15u) & ~15ull; }
@@ -299,6 +342,16 @@ void free_host_path(cas_ctx* c) {
         if (ev) { cudaEventDestroy(ev); ev = nullptr; }
 }
 
+void ensure_pack_pool(cas_ctx* ctx) {
+    if (ctx->pool) return;
+    int n = ctx->pack_threads;
+    if (n <= 0) {  // half the cores, at most 8: measured best on a 16-core host (50 vs 42 GB/s with 16)
+        n = (int)std::thread::hardware_concurrency() / 2;
+        n = std::max(1, std::min(n, 8));
+    }
+    ctx->pool = new PackPool(n);
+}
+
 // Grow-only resources of the host path: nothing is allocated per call once the
 // largest batch shape has been seen.
 int ensure_host_path(cas_ctx* ctx, uint64_t arena_bytes, uint64_t stage_bytes, uint64_t objs) {
@@ -310,14 +363,7 @@ int ensure_host_path(cas_ctx* ctx, uint64_t arena_bytes, uint64_t stage_bytes, u
             if (!ev) CU(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
     for (auto& ev : ctx->ev_join)
         if (!ev) CU(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
-    if (!ctx->pool) {
-        int n = ctx->pack_threads;
-        if (n <= 0) {  // half the cores, at most 8: measured best on a 16-core host (50 vs 42 GB/s with 16)
-            n = (int)std::thread::hardware_concurrency() / 2;
-            n = std::max(1, std::min(n, 8));
-        }
-        ctx->pool = new PackPool(n);
-    }
+    ensure_pack_pool(ctx);
     if (arena_bytes > ctx->arena_cap) {
         if (ctx->d_arena) cudaFree(ctx->d_arena);
         ctx->d_arena = nullptr; ctx->arena_cap = 0;
@@ -421,6 +467,7 @@ int cas_create(int device, cas_ctx** out) {
     if (const char* v = getenv("B200CAS_KERNEL")) ctx->kernel = std::max(0, std::min(2, atoi(v)));
     if (const char* v = getenv("B200CAS_FMA")) ctx->fma_level = std::max(0, std::min(4, atoi(v)));
     if (const char* v = getenv("B200CAS_CTAS")) ctx->ctas_per_sm = atoi(v) == 0 ? 0 : std::max(2, std::min(4, atoi(v)));
+    if (const char* v = getenv("B200CAS_TRACE")) ctx->trace = atoi(v) != 0;
     *out = ctx;
     return CAS_OK;
 }
@@ -435,6 +482,7 @@ void cas_destroy(cas_ctx* ctx) {
     if (ctx->s_copy) cudaStreamDestroy(ctx->s_copy);
     if (ctx->d_sink) cudaFree(ctx->d_sink);
     delete ctx->pool;
+    delete ctx->io_pool;
     delete ctx;
 }
 
@@ -477,6 +525,23 @@ int cas_set_option(cas_ctx* ctx, int key, int64_t v) {
             if (v != 0 && (v < 2 || v > 4)) return fail(ctx, CAS_E_ARG, "CAS_OPT_CTAS_PER_SM must be 0 (auto), 2, 3 or 4");
             ctx->ctas_per_sm = (int)v;
             return CAS_OK;
+        case CAS_OPT_LONG_MAX_PER_WARP:
+            if (v != 1 && v != 2 && v != 4 && v != 8 && v != 16 && v != 32)
+                return fail(ctx, CAS_E_ARG, "CAS_OPT_LONG_MAX_PER_WARP must be 1, 2, 4, 8, 16 or 32");
+            ctx->long_max_m = (int)v;
+            return CAS_OK;
+        case CAS_OPT_FIRST_CHUNK_BYTES:
+            if (v < 65536) return fail(ctx, CAS_E_ARG, "CAS_OPT_FIRST_CHUNK_BYTES must be >= 64 KiB");
+            ctx->first_chunk = ((uint64_t)v + 65535) & ~65535ull;
+            return CAS_OK;
+        case CAS_OPT_IO_THREADS:
+            if (v < 1 || v > 256) return fail(ctx, CAS_E_ARG, "CAS_OPT_IO_THREADS must be 1..256");
+            if (ctx->io_pool && ctx->io_pool->size() != (int)v) {
+                delete ctx->io_pool;
+                ctx->io_pool = nullptr;
+            }
+            ctx->io_threads = (int)v;
+            return CAS_OK;
     }
     return fail(ctx, CAS_E_ARG, "unknown option key");
 }
@@ -492,6 +557,9 @@ int cas_get_option(const cas_ctx* ctx, int key, int64_t* v) {
         case CAS_OPT_ARENA_BYTES: *v = (int64_t)ctx->arena_max; return CAS_OK;
         case CAS_OPT_LONG_MAX_OBJECTS: *v = (int64_t)ctx->long_max_objects; return CAS_OK;
         case CAS_OPT_LONG_MIN_BYTES: *v = (int64_t)ctx->long_min_bytes; return CAS_OK;
+        case CAS_OPT_LONG_MAX_PER_WARP: *v = ctx->long_max_m; return CAS_OK;
+        case CAS_OPT_FIRST_CHUNK_BYTES: *v = (int64_t)ctx->first_chunk; return CAS_OK;
+        case CAS_OPT_IO_THREADS: *v = ctx->io_pool ? ctx->io_pool->size() : ctx->io_threads; return CAS_OK;
     }
     return CAS_E_ARG;
 }
@@ -535,7 +603,10 @@ int cas_hash_device_long(cas_ctx* ctx, const void* d_base, const uint64_t* d_off
     a.order = d_order;
     a.n = n;
     a.out = static_cast<uint8_t*>(d_out);
-    return launch_long(ctx, a, static_cast<cudaStream_t>(stream));
+    // As many objects per warp as it takes to keep to about one warp per SM sub-partition.
+    int m = 1;
+    while (m < ctx->long_max_m && (uint64_t)m * std::max<uint64_t>(ctx->long_max_objects, 1) < n) m *= 2;
+    return launch_long(ctx, a, static_cast<cudaStream_t>(stream), m);
 }
 
 int cas_hash_device_uniform(cas_ctx* ctx, const void* d_base, uint64_t stride, uint64_t len, uint64_t n,
@@ -552,9 +623,7 @@ int cas_hash_device_uniform(cas_ctx* ctx, const void* d_base, uint64_t stride, u
     a.n = n;
     a.out = static_cast<uint8_t*>(d_out);
     // Few long objects: lane-per-object would leave the GPU empty and every chain slow.
-    if (n <= ctx->long_max_objects && len >= ctx->long_min_bytes)
-        return launch_long(ctx, a, static_cast<cudaStream_t>(stream));
-    return launch_batch(ctx, a, static_cast<cudaStream_t>(stream));
+    return launch_group(ctx, a, len, static_cast<cudaStream_t>(stream));
 }
 
 int cas_gen_synthetic(cas_ctx* ctx, void* d_dst, uint64_t seed, uint64_t first_obj, uint64_t n, uint64_t len,
@@ -643,10 +712,172 @@ bool read_file_range(const char* path, uint64_t offset, uint8_t* dst, uint64_t b
     return done == bytes;
 }
 
-int hash_host_impl(cas_ctx* ctx, const ByteSource& srcs, const uint64_t* len, uint64_t n, uint8_t* out) {
+// ------------------------------------------------------------------ store-side file helpers --
+void ensure_io_pool(cas_ctx* ctx) {
+    if (ctx->io_pool) return;
+    int n = ctx->io_threads;
+    if (n <= 0) n = std::max(1, std::min((int)std::thread::hardware_concurrency() / 2, 8));
+    ctx->io_pool = new PackPool(n);
+}
+
+// mkdir -p
+bool make_dirs(const char* dir) {
+    struct stat sb;
+    if (stat(dir, &sb) == 0) return S_ISDIR(sb.st_mode);
+    std::string p(dir);
+    for (size_t i = 1; i <= p.size(); ++i) {
+        if (i != p.size() && p[i] != '/') continue;
+        const std::string part = p.substr(0, i);
+        if (mkdir(part.c_str(), 0777) != 0 && errno != EEXIST) return false;
+    }
+    return stat(dir, &sb) == 0 && S_ISDIR(sb.st_mode);
+}
+
+uint64_t fresh_token() {
+    static std::atomic<uint64_t> counter{0};
+    uint64_t t = 0;
+    const int fd = open("/dev/urandom", O_RDONLY | O_CLOEXEC);
+    if (fd >= 0) {
+        if (read(fd, &t, sizeof t) != (ssize_t)sizeof t) t = 0;
+        close(fd);
+    }
+    struct timeval tv;
+    gettimeofday(&tv, nullptr);
+    return t ^ ((uint64_t)getpid() << 40) ^ ((uint64_t)tv.tv_usec << 20) ^ (uint64_t)tv.tv_sec ^ (counter.fetch_add(1) << 56);
+}
+
+// Temporary names start with '.', which no object id can (the reference's Hash pattern,
+// utils/validation.py:19), so a reader can never mistake a half-written file for an object.
+void tmp_name(char* dst, size_t cap, uint64_t token, uint64_t i) {
+    snprintf(dst, cap, ".tmp-%016llx-%llu", (unsigned long long)token, (unsigned long long)i);
+}
+
+bool write_whole_file(const char* path, const uint8_t* src, uint64_t bytes) {
+    const int fd = open(path, O_WRONLY | O_CREAT | O_EXCL | O_CLOEXEC, 0666);
+    if (fd < 0) return false;
+    uint64_t done = 0;
+    while (done < bytes) {
+        const ssize_t w = write(fd, src + done, bytes - done);
+        if (w < 0) {
+            if (errno == EINTR) continue;
+            break;
+        }
+        done += (uint64_t)w;
+    }
+    const bool ok = close(fd) == 0 && done == bytes;
+    if (!ok) unlink(path);
+    return ok;
+}
+
+void hex_name(char* dst, const uint8_t* digest) {
+    static const char* H = "0123456789abcdef";
+    for (int i = 0; i < 32; ++i) { dst[2 * i] = H[digest[i] >> 4]; dst[2 * i + 1] = H[digest[i] & 15]; }
+    dst[64] = 0;
+}
+
+// Gives `tmp` its final name unless that name is taken: 0 = renamed, 1 = an object with this
+// id was there already (tmp removed), < 0 = error (tmp removed).  Never replaces a file, so a
+// reader holding the existing object open is not disturbed, and the final name only ever
+// appears complete (rename is atomic).
+int rename_noreplace(const char* tmp, const char* target) {
+#if defined(SYS_renameat2)
+    if (syscall(SYS_renameat2, AT_FDCWD, tmp, AT_FDCWD, target, 1u /* RENAME_NOREPLACE */) == 0) return CAS_STORED_NEW;
+    if (errno == EEXIST) { unlink(tmp); return CAS_STORED_EXISTED; }
+    if (errno != EINVAL && errno != ENOSYS) { unlink(tmp); return CAS_E_IO; }
+#endif
+    if (link(tmp, target) == 0) { unlink(tmp); return CAS_STORED_NEW; }  // file systems without RENAME_NOREPLACE
+    const int err = errno;
+    unlink(tmp);
+    return err == EEXIST ? CAS_STORED_EXISTED : CAS_E_IO;
+}
+
+// Final names for a batch: tmp files made by cas_store_host (paths == NULL: names from the
+// token) or the caller's spool files.  Objects whose status is already negative are skipped
+// (their tmp file is removed if it is ours).
+void publish_tmp_files(cas_ctx* ctx, const std::string& root, uint64_t token, const char* const* paths, uint64_t n,
+                       const uint8_t* digests, int32_t* status) {
+    std::atomic<uint64_t> next{0};
+    const std::function<void(int)> job = [&](int) {
+        char name[64], hex[65];
+        for (;;) {
+            const uint64_t i = next.fetch_add(1, std::memory_order_relaxed);
+            if (i >= n) return;
+            std::string tmp;
+            if (paths) {
+                tmp = paths[i];
+            } else {
+                tmp_name(name, sizeof name, token, i);
+                tmp = root + "/" + name;
+            }
+            if (status[i] < 0) {
+                if (!paths) unlink(tmp.c_str());
+                continue;
+            }
+            hex_name(hex, digests + 32 * i);
+            status[i] = rename_noreplace(tmp.c_str(), (root + "/" + hex).c_str());
+        }
+    };
+    ctx->io_pool->run(job);
+}
+
+void remove_tmp_files(cas_ctx* ctx, const std::string& root, uint64_t token, uint64_t n) {
+    std::atomic<uint64_t> next{0};
+    const std::function<void(int)> job = [&](int) {
+        char name[64];
+        for (;;) {
+            const uint64_t i = next.fetch_add(1, std::memory_order_relaxed);
+            if (i >= n) return;
+            tmp_name(name, sizeof name, token, i);
+            unlink((root + "/" + name).c_str());
+        }
+    };
+    ctx->io_pool->run(job);
+}
+
+// Sizes of n files, looked up by the pack pool's threads.  With status == NULL a file that is
+// missing or not regular fails the call; otherwise it gets status CAS_E_IO and length 0.
+int stat_files(cas_ctx* ctx, const char* const* paths, uint64_t n, uint64_t* len, int32_t* status) {
+    ensure_pack_pool(ctx);
+    std::atomic<uint64_t> next{0};
+    std::atomic<int64_t> first_bad{-1};
+    const std::function<void(int)> job = [&](int) {
+        for (;;) {
+            const uint64_t i0 = next.fetch_add(64, std::memory_order_relaxed);
+            if (i0 >= n) return;
+            for (uint64_t i = i0; i < std::min(n, i0 + 64); ++i) {
+                struct stat sb;
+                if (paths[i] && stat(paths[i], &sb) == 0 && S_ISREG(sb.st_mode)) {
+                    len[i] = (uint64_t)sb.st_size;
+                } else {
+                    len[i] = 0;
+                    if (status) status[i] = CAS_E_IO;
+                    int64_t expect = -1;
+                    first_bad.compare_exchange_strong(expect, (int64_t)i);
+                }
+            }
+        }
+    };
+    ctx->pool->run(job);
+    if (!status && first_bad.load() >= 0) {
+        const char* bad = paths[first_bad.load()];
+        char msg[400];
+        snprintf(msg, sizeof msg, "cas_hash_files: cannot stat regular file '%.300s'", bad ? bad : "(null)");
+        return fail(ctx, CAS_E_IO, msg);
+    }
+    return CAS_OK;
+}
+
+double now_s() {
+    return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+int hash_host_impl(cas_ctx* ctx, const ByteSource& srcs, const uint64_t* len, uint64_t n, uint8_t* out,
+                   int32_t* status = nullptr) {
     const uint8_t* hbase = srcs.hbase;
     const uint64_t* off = srcs.off;
     const bool from_files = srcs.paths != nullptr;
+    const double t_begin = ctx->trace ? now_s() : 0.0;
+    double t_pack = 0.0, t_stage_wait = 0.0;
     // A call that failed half-way may have left copies and kernels in flight on buffers
     // this call is about to reuse: wait them out before touching anything.
     if (ctx->host_path_dirty) CU(cudaDeviceSynchronize());
@@ -678,15 +909,18 @@ int hash_host_impl(cas_ctx* ctx, const ByteSource& srcs, const uint64_t* len, ui
         }
     }
 
-    // Chunk (copy granule) and arena sizes.  Small batches are cut finer so that copy
-    // and hash still overlap; the arena has two halves so that the copies of one epoch
-    // run while the kernels of the previous one finish.
-    uint64_t chunk = std::min<uint64_t>(ctx->wave_bytes, std::max<uint64_t>(8 * MiB, (total / 8 + MiB - 1) & ~(MiB - 1)));
+    // Chunk (copy granule) and arena sizes.  The first chunk is small so that the first
+    // copy and the first kernel start almost at once; chunks then double up to a cap that
+    // keeps at least ~8 of them in a batch (copy and hash overlap) and at most wave_bytes.
+    // The arena has two halves so that the copies of one epoch run while the kernels of
+    // the previous one finish.
+    const uint64_t chunk_cap = std::min<uint64_t>(ctx->wave_bytes, std::max<uint64_t>(8 * MiB, (total / 8 + MiB - 1) & ~(MiB - 1)));
+    uint64_t chunk_now = std::min<uint64_t>(chunk_cap, ctx->first_chunk);
     uint64_t half = std::max<uint64_t>(std::min<uint64_t>(ctx->arena_max / 2, (total + MiB - 1) & ~(MiB - 1)),
                                        std::max<uint64_t>(align16(maxlen), 16));
     half = (half + 255) & ~255ull;
     const bool one_epoch = total <= half;
-    int rc = ensure_host_path(ctx, one_epoch ? half : 2 * half, chunk, n);
+    int rc = ensure_host_path(ctx, one_epoch ? half : 2 * half, chunk_cap, n);
     if (rc) return rc;
     const bool pinned_src = !from_files && host_ptr_is_pinned(hbase);
 
@@ -712,6 +946,7 @@ int hash_host_impl(cas_ctx* ctx, const ByteSource& srcs, const uint64_t* len, ui
     CU(cudaMemcpyAsync(ctx->d_meta, h_off, n * 8, cudaMemcpyHostToDevice, ctx->s_copy));
     CU(cudaMemcpyAsync(ctx->d_meta + n, h_len, n * 8, cudaMemcpyHostToDevice, ctx->s_copy));
     for (auto& st : ctx->stage) st.used = false;
+    const double t_prep = ctx->trace ? now_s() : 0.0;
 
     // A run of bytes of one object: from memory (src) or from file `obj` at `fpos`.
     struct Piece { const uint8_t* src; uint64_t dst; uint64_t bytes; uint64_t obj; uint64_t fpos; };
@@ -726,8 +961,9 @@ int hash_host_impl(cas_ctx* ctx, const ByteSource& srcs, const uint64_t* len, ui
         const uint64_t bytes = h_off[k1 - 1] + align16(h_len[k1 - 1]);
         uint64_t kp = k0;       // first object that still has bytes to copy
         uint64_t klaunch = k0;  // first object not yet handed to a kernel
-        for (uint64_t c0 = 0; c0 < bytes || klaunch < k1; c0 += chunk) {
-            const uint64_t c1 = std::min(bytes, c0 + chunk);
+        for (uint64_t c0 = 0; c0 < bytes || klaunch < k1;) {
+            const uint64_t c1 = std::min(bytes, c0 + chunk_now);
+            chunk_now = std::min(chunk_cap, chunk_now * 2);
             Stage& sg = ctx->stage[chunk_no % NSTG];
             // Pieces of objects that fall into [c0, c1), merged when contiguous on both sides.
             pieces.clear();
@@ -751,7 +987,9 @@ int hash_host_impl(cas_ctx* ctx, const ByteSource& srcs, const uint64_t* len, ui
                     for (auto& pc : pieces)
                         CU(cudaMemcpyAsync(d_base + pc.dst, pc.src, pc.bytes, cudaMemcpyHostToDevice, ctx->s_copy));
                 } else if (!pieces.empty()) {
+                    const double tw0 = ctx->trace ? now_s() : 0.0;
                     if (sg.used) CU(cudaEventSynchronize(sg.ev));  // its previous H2D has left the staging
+                    const double tw1 = ctx->trace ? now_s() : 0.0;
                     const int T = ctx->pool->size();
                     const uint64_t span = c1 - c0, share = ((span + T - 1) / (uint64_t)T + 63) & ~63ull;
                     uint8_t* stage = sg.h;
@@ -766,11 +1004,20 @@ int hash_host_impl(cas_ctx* ctx, const ByteSource& srcs, const uint64_t* len, ui
                             const uint64_t a = std::max(pv[i].dst, lo), b = std::min(pv[i].dst + pv[i].bytes, hi);
                             if (pv[i].src) {
                                 memcpy(stage + (a - c0), pv[i].src + (a - pv[i].dst), b - a);
+                            } else if (status && status[pv[i].obj] < 0) {
+                                memset(stage + (a - c0), 0, b - a);  // already failed: keep the staging defined
                             } else if (!read_file_range(srcs.paths[pv[i].obj], pv[i].fpos + (a - pv[i].dst), stage + (a - c0), b - a)) {
-                                io_failed.store(true);  // shorter than stat() said, or unreadable
+                                // shorter than stat() said, or unreadable
+                                if (status) {
+                                    status[pv[i].obj] = CAS_E_IO;  // this object only; its digest is not reported
+                                    memset(stage + (a - c0), 0, b - a);
+                                } else {
+                                    io_failed.store(true);
+                                }
                             }
                         }
                     });
+                    if (ctx->trace) { t_stage_wait += tw1 - tw0; t_pack += now_s() - tw1; }
                     if (io_failed.load()) {
                         cudaDeviceSynchronize();
                         return fail(ctx, CAS_E_IO, "a file changed or could not be read while it was being hashed");
@@ -786,7 +1033,7 @@ int hash_host_impl(cas_ctx* ctx, const ByteSource& srcs, const uint64_t* len, ui
             while (kend < k1 && h_off[kend] + h_len[kend] <= c1) ++kend;
             if (c1 >= bytes) kend = k1;
             while (kend > klaunch) {
-                // [klaunch, split) goes one warp per object, [split, kend) one lane per object.
+                // [klaunch, split) goes one warp per object, [split, kend) by group size.
                 const bool is_long = klaunch < n_long;
                 const uint64_t split = is_long ? std::min(kend, n_long) : kend;
                 cudaStream_t cs = ctx->s_comp[launch_no % NCOMP];
@@ -797,19 +1044,25 @@ int hash_host_impl(cas_ctx* ctx, const ByteSource& srcs, const uint64_t* len, ui
                 a.len = ctx->d_meta + n + klaunch;
                 a.n = split - klaunch;
                 a.out = ctx->d_dig + 32ull * klaunch;
-                if ((rc = is_long ? launch_long(ctx, a, cs) : launch_batch(ctx, a, cs))) return rc;
+                // objects are in descending order of compressions: the group's last one is (within 63 bytes) its shortest
+                const uint64_t min_len = h_len[split - 1] & ~63ull;
+                if ((rc = is_long ? launch_long(ctx, a, cs, 1) : launch_group(ctx, a, min_len, cs))) return rc;
                 ++launch_no;
                 klaunch = split;
             }
             if (c1 >= bytes) break;
+            c0 = c1;
         }
-        for (int i = 0; i < NCOMP; ++i) CU(cudaEventRecord(ctx->ev_epoch[e & 1][i], ctx->s_comp[i]));
+        if (e + 3 < epoch_first.size())  // a later epoch will reuse this half
+            for (int i = 0; i < NCOMP; ++i) CU(cudaEventRecord(ctx->ev_epoch[e & 1][i], ctx->s_comp[i]));
     }
-    // Join the compute streams, bring the digests back, restore the caller's order.
-    for (int i = 1; i < NCOMP; ++i) {
+    // Join the compute streams that were used, bring the digests back, restore the caller's order.
+    const int used_streams = (int)std::min<uint64_t>(launch_no, NCOMP);
+    for (int i = 1; i < used_streams; ++i) {
         CU(cudaEventRecord(ctx->ev_join[i], ctx->s_comp[i]));
         CU(cudaStreamWaitEvent(ctx->s_comp[0], ctx->ev_join[i], 0));
     }
+    const double t_issued = ctx->trace ? now_s() : 0.0;
     CU(cudaMemcpyAsync(ctx->h_dig, ctx->d_dig, n * 32, cudaMemcpyDeviceToHost, ctx->s_comp[0]));
     CU(cudaStreamSynchronize(ctx->s_comp[0]));
     CU(cudaStreamSynchronize(ctx->s_copy));
@@ -819,6 +1072,16 @@ int hash_host_impl(cas_ctx* ctx, const ByteSource& srcs, const uint64_t* len, ui
         for (uint64_t k = 0; k < n; ++k) memcpy(out + 32ull * order[k], ctx->h_dig + 32ull * k, 32);
     }
     ctx->host_path_dirty = false;
+    if (ctx->trace) {
+        const double t_end = now_s();
+        fprintf(stderr,
+                "{\"b200cas_trace\": \"host_path\", \"objects\": %llu, \"bytes\": %llu, \"chunks\": %llu, \"launches\": %llu, "
+                "\"pinned_src\": %s, \"files\": %s, \"ms_total\": %.3f, \"ms_prepare\": %.3f, \"ms_pack\": %.3f, "
+                "\"ms_wait_for_staging\": %.3f, \"ms_issue_other\": %.3f, \"ms_final_wait\": %.3f}\n",
+                (unsigned long long)n, (unsigned long long)total, (unsigned long long)chunk_no, (unsigned long long)launch_no,
+                pinned_src ? "true" : "false", from_files ? "true" : "false", (t_end - t_begin) * 1e3, (t_prep - t_begin) * 1e3,
+                t_pack * 1e3, t_stage_wait * 1e3, (t_issued - t_prep - t_pack - t_stage_wait) * 1e3, (t_end - t_issued) * 1e3);
+    }
     return CAS_OK;
 }
 
@@ -846,19 +1109,90 @@ int cas_hash_files(cas_ctx* ctx, const char* const* paths, uint64_t n, void* out
     if (n > 0xFFFFFFFFull) return fail(ctx, CAS_E_ARG, "cas_hash_files: more than 2^32-1 files in one call");
     CU(cudaSetDevice(ctx->device));
     std::vector<uint64_t> len(n);
-    for (uint64_t i = 0; i < n; ++i) {
-        struct stat sb;
-        if (!paths[i] || stat(paths[i], &sb) != 0 || !S_ISREG(sb.st_mode)) {
-            char msg[400];
-            snprintf(msg, sizeof msg, "cas_hash_files: cannot stat regular file '%.300s'", paths[i] ? paths[i] : "(null)");
-            return fail(ctx, CAS_E_IO, msg);
-        }
-        len[i] = (uint64_t)sb.st_size;
-    }
+    int rc = stat_files(ctx, paths, n, len.data(), nullptr);
+    if (rc) return rc;
     if (sizes_out) memcpy(sizes_out, len.data(), n * sizeof(uint64_t));
     ByteSource src;
     src.paths = paths;
     return hash_host_impl(ctx, src, len.data(), n, static_cast<uint8_t*>(out32n));
+}
+
+int cas_reserve(cas_ctx* ctx, uint64_t batch_bytes, uint64_t max_objects) {
+    if (!ctx) return CAS_E_ARG;
+    CU(cudaSetDevice(ctx->device));
+    if (ctx->host_path_dirty) CU(cudaDeviceSynchronize());
+    const uint64_t total = std::max<uint64_t>(batch_bytes, MiB);
+    const uint64_t chunk_cap = std::min<uint64_t>(ctx->wave_bytes, std::max<uint64_t>(8 * MiB, (total / 8 + MiB - 1) & ~(MiB - 1)));
+    uint64_t half = std::min<uint64_t>(ctx->arena_max / 2, (total + MiB - 1) & ~(MiB - 1));
+    half = (half + 255) & ~255ull;
+    return ensure_host_path(ctx, total <= half ? half : 2 * half, chunk_cap, std::max<uint64_t>(max_objects, 1));
+}
+
+int cas_store_host(cas_ctx* ctx, const char* dir, const void* base, const uint64_t* off, const uint64_t* len,
+                   uint64_t n, void* out32n, int32_t* status_out) {
+    if (!ctx) return CAS_E_ARG;
+    if (n == 0) return CAS_OK;
+    if (!dir || !off || !len || !out32n) return fail(ctx, CAS_E_ARG, "cas_store_host: NULL directory/offset/length/output array");
+    if (n > 0xFFFFFFFFull) return fail(ctx, CAS_E_ARG, "cas_store_host: more than 2^32-1 objects in one call");
+    CU(cudaSetDevice(ctx->device));
+    if (!make_dirs(dir)) return fail(ctx, CAS_E_IO, "cas_store_host: cannot create the store directory");
+    ensure_io_pool(ctx);
+    std::vector<int32_t> local_status;
+    int32_t* status = status_out;
+    if (!status) { local_status.resize(n); status = local_status.data(); }
+    for (uint64_t i = 0; i < n; ++i) status[i] = CAS_STORED_NEW;
+    const uint8_t* hbase = static_cast<const uint8_t*>(base);
+    const std::string root(dir);
+    const uint64_t token = fresh_token();
+
+    // File writers run while this thread drives the GPU pipeline over the same bytes.
+    std::atomic<uint64_t> next{0};
+    const std::function<void(int)> write_all = [&](int) {
+        char name[64];
+        for (;;) {
+            const uint64_t i = next.fetch_add(1, std::memory_order_relaxed);
+            if (i >= n) return;
+            tmp_name(name, sizeof name, token, i);
+            if (!write_whole_file((root + "/" + name).c_str(), hbase + off[i], len[i])) status[i] = CAS_E_IO;
+        }
+    };
+    ctx->io_pool->start(write_all);
+    ByteSource src;
+    src.hbase = hbase;
+    src.off = off;
+    const int rc = hash_host_impl(ctx, src, len, n, static_cast<uint8_t*>(out32n));
+    ctx->io_pool->wait();
+    if (rc) {  // no ids: nothing may appear under a final name
+        remove_tmp_files(ctx, root, token, n);
+        return rc;
+    }
+    publish_tmp_files(ctx, root, token, nullptr, n, static_cast<const uint8_t*>(out32n), status);
+    return CAS_OK;
+}
+
+int cas_publish_files(cas_ctx* ctx, const char* dir, const char* const* paths, uint64_t n, void* out32n,
+                      uint64_t* sizes_out, int32_t* status_out) {
+    if (!ctx) return CAS_E_ARG;
+    if (n == 0) return CAS_OK;
+    if (!paths || !out32n || !status_out) return fail(ctx, CAS_E_ARG, "cas_publish_files: NULL path, output or status array");
+    if (n > 0xFFFFFFFFull) return fail(ctx, CAS_E_ARG, "cas_publish_files: more than 2^32-1 files in one call");
+    CU(cudaSetDevice(ctx->device));
+    if (dir && !make_dirs(dir)) return fail(ctx, CAS_E_IO, "cas_publish_files: cannot create the store directory");
+    ensure_io_pool(ctx);
+    for (uint64_t i = 0; i < n; ++i) status_out[i] = CAS_STORED_NEW;
+    std::vector<uint64_t> len(n);
+    int rc = stat_files(ctx, paths, n, len.data(), status_out);  // a missing file fails that file only
+    if (rc) return rc;
+    if (sizes_out) memcpy(sizes_out, len.data(), n * sizeof(uint64_t));
+    ByteSource src;
+    src.paths = paths;
+    rc = hash_host_impl(ctx, src, len.data(), n, static_cast<uint8_t*>(out32n), status_out);
+    if (rc) return rc;
+    uint8_t* out = static_cast<uint8_t*>(out32n);
+    for (uint64_t i = 0; i < n; ++i)
+        if (status_out[i] < 0) memset(out + 32 * i, 0, 32);  // never a digest of bytes that were not all read
+    if (dir) publish_tmp_files(ctx, std::string(dir), 0, paths, n, out, status_out);
+    return CAS_OK;
 }
 
 // ---------------------------------------------------------------------------

@@ -1,4 +1,4 @@
-// Long messages, few of them: one WARP per M messages (M = 1, 2, 4, 8, 16).
+// Long messages, few of them: one WARP per M messages (M = 1, 2, 4, 8, 16, 32).
 //
 // With lane-per-message a batch of a few large objects (BASELINE config 5, the big
 // files of config 4, a single upload) leaves the GPU almost empty and every chain
@@ -14,14 +14,17 @@
 //            the serial path instead of ~27.
 // One warp instruction of phase B advances M chains at once, so M trades per-chain
 // speed (phase A is amortised over 32 / M blocks per chain) against chains per
-// sub-partition: M = 1 is fastest per chain (BASELINE config 5, <= 592 objects), M = 2..16
-// fill the window up to ~9 500 objects where one lane per object would run each chain
-// alone on a sub-partition at ~60 % of this rate.  The digest is unchanged.
+// sub-partition.  Measured on a B200 (profiles/r02_kbench_long.jsonl, 1 MiB objects, one
+// warp per sub-partition): M = 1 70-74 MB/s per chain, M = 2 69, M = 4 66, M = 8 61,
+// M = 16 52, M = 32 41, against 31 MB/s for one object per lane (kernel_ldg) -- so the warp
+// form wins up to ~38 000 long objects and the engine picks M from the object count.
+// The digest is unchanged.
 //
-// The serial path is bounded by one warp's ALU-pipe occupancy: a warp instruction takes
-// the 16-lane ALU pipe of its sub-partition for two clocks whatever its active mask
-// (measured: tools/kbench_long.cu ACT variants), and a round needs 10 logic instructions
-// that no other pipe can execute.
+// The serial path is bounded by one warp's ALU-pipe occupancy: ptxas' schedule of the 64
+// rounds is 11 ALU-pipe instructions per round (6 SHF + 4 LOP3 + 1 IADD3; the other adds
+// run as IMAD on the FMA pipe), issued every second clock.  A warp instruction takes the
+// pipe for two clocks whatever its active mask (phase B on 16, 8 or 1 lanes: same time),
+// and rotations moved to the FMA pipe (IMAD + IMAD.HI) are slower than the SHF they save.
 #pragma once
 #include "sha256_batch.cuh"
 
@@ -98,7 +101,7 @@ __device__ __forceinline__ void long_round(uint32_t a, uint32_t b, uint32_t c, u
 // the first ACT lanes run phase B.
 template <int FMA_LEVEL, int ADDS, int M = 1, int ACT = 32, int ROTF = 0>
 __global__ void __launch_bounds__(32) kernel_long(const BatchArgs A) {
-    static_assert(M == 1 || M == 2 || M == 4 || M == 8 || M == 16 || M == 32, "M must divide 32");
+    static_assert(M == 1 || M == 2 || M == 4 || M == 8 || M == 16 || M == 32, "M must be a power of two up to 32");
     static_assert(ACT == 32 || M == 1, "ACT is an experiment knob of the one-message form");
     constexpr int G = 32 / M;
     extern __shared__ __align__(16) uint8_t smem_long[];

@@ -165,6 +165,46 @@ class GpuHasher:
     def hash_one(self, data: BytesLike) -> str:
         return self.hash_many([data])[0]
 
+    def reserve(self, batch_bytes: int, max_objects: int) -> None:
+        """Allocate the host path's buffers now for batches up to this size (cas_reserve), so the
+        first request does not pay for cudaMalloc / cudaHostAlloc."""
+        with self._lock:
+            self._check(self._lib.cas_reserve(self._ctx, int(batch_bytes), int(max_objects)))
+
+    # -- hashing and storing in one call (the Storage-shaped path) ----------------------------
+    def store_many(self, root: str | os.PathLike, objs: Sequence[BytesLike]) -> tuple[list[str], np.ndarray]:
+        """Hash a batch and store every object as ``<root>/<id>`` (cas_store_host: file writers run
+        beside the GPU pipeline, final names by atomic rename).  Returns (ids, status) with status
+        0 = stored now, 1 = an object of that id was there already, < 0 = that object failed."""
+        n = len(objs)
+        status = np.zeros(n, dtype=np.int32)
+        if n == 0:
+            return [], status
+        addr, length, keep = _addresses(objs)
+        out = np.empty((n, 32), dtype=np.uint8)
+        with self._lock:
+            self._check(self._lib.cas_store_host(self._ctx, os.fsencode(root), None, addr.ctypes.data, length.ctypes.data, n,
+                                                 out.ctypes.data, status.ctypes.data))
+        del keep
+        return hex_ids(out), status
+
+    def publish_files(self, root: str | os.PathLike | None, paths: Sequence[str | os.PathLike]):
+        """Hash files and rename each to ``<root>/<id>`` (cas_publish_files); with ``root`` None
+        they are only hashed.  A file that cannot be read fails alone.  Returns (ids, sizes, status)."""
+        n = len(paths)
+        out = np.empty((n, 32), dtype=np.uint8)
+        sizes = np.zeros(n, dtype=np.uint64)
+        status = np.zeros(n, dtype=np.int32)
+        if n == 0:
+            return [], sizes, status
+        raw = [os.fsencode(p) for p in paths]
+        arr = (ctypes.c_char_p * n)(*raw)
+        with self._lock:
+            self._check(self._lib.cas_publish_files(self._ctx, None if root is None else os.fsencode(root),
+                                                    ctypes.cast(arr, ctypes.c_void_p), n, out.ctypes.data, sizes.ctypes.data,
+                                                    status.ctypes.data))
+        return hex_ids(out), sizes, status
+
     # -- device buffers (kernel-only path) ------------------------------------
     def digest_device(self, base, off, length, order=None, out=None, stream=None, warp_per_object=False):
         """Hash objects resident in device memory. ``base`` is a CUDA uint8 tensor (or

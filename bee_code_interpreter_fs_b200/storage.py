@@ -11,20 +11,23 @@ Consequences of content-derived ids:
   to a temporary file and renames it to ``<dir>/<sha256hex>`` on close;
   ``.hash`` is set at close, which is when the reference's caller reads it
   (services/kubernetes_code_executor.py:146);
-* equal content gives equal ids: a second write of the same bytes is a no-op;
-* ``delete`` removes the file, as in the reference; because equal content now shares
-  one file, ``Storage(..., refcount=True)`` keeps a per-object holder count instead
-  (one ``write`` = one holder) and only the last ``delete`` unlinks.
+* equal content gives equal ids: a second write of the same bytes stores nothing new;
+* because equal content shares one file, every write counts as one *holder* of the object
+  and ``delete`` (storage.py:92-101; reached over HTTP by ``DELETE /v1/files/{hash}`` and
+  ``GET ...?delete=true``, http_server.py:88-109) removes the file only when the last
+  holder lets go -- otherwise one client's delete would take the object away from every
+  other client that uploaded the same bytes, which the reference's random ids cannot do.
+  ``refcount=False`` gives the reference's literal behaviour (first delete unlinks).
 
-With the GPU hasher a streaming writer keeps nothing in memory: chunks go to the spool file and
-the engine reads that file itself at close (``cas_hash_files``: pread into pinned staging).
-
-Concurrent finalisations (the ``asyncio.gather`` over changed files at
+The work of a batch -- hashing, writing the bytes out, giving files their final names --
+happens in one C call per batch (``cas_store_host`` for in-memory objects,
+``cas_publish_files`` for spooled writers: include/b200cas.h) on a worker thread, off the
+event loop.  Concurrent calls (the ``asyncio.gather`` over changed files at
 kubernetes_code_executor.py:149-154) are coalesced by ``_Batcher`` (group commit: no added
 latency for a lone writer, one engine call for everything that queued up behind a running
-one; ``batch_window`` optionally waits to collect more).  The blocking CUDA call runs in a
-worker thread, off the event loop, and the same worker gives each object its final name, so
-a batch of N writes costs one thread hop, not N.
+one; ``batch_window`` optionally waits to collect more).  A request that fails (its spool
+file vanished, the disk is full) fails alone; a request whose caller was cancelled before
+its batch started is dropped from the batch.
 Additive API: ``hash_many``, ``write_many``, ``verify``, ``verify_all``.
 """
 from __future__ import annotations
@@ -35,7 +38,6 @@ import re
 import secrets
 import threading
 from contextlib import asynccontextmanager
-from functools import partial
 from typing import AsyncIterator, Callable, Protocol, Sequence
 
 from anyio import Path
@@ -45,6 +47,8 @@ from .hasher import GpuHasher
 from .validation import HASH_PATTERN, Hash
 
 _ID_RE = re.compile(HASH_PATTERN)
+
+_HASH, _STORE, _PUBLISH = "hash", "store", "publish"  # what a queued request wants done
 
 
 class ObjectReader(Protocol):
@@ -58,23 +62,21 @@ class ObjectWriter(Protocol):
 
 
 class _Request:
-    __slots__ = ("payload", "is_path", "future", "on_done")
+    __slots__ = ("payload", "kind", "future")
 
-    def __init__(self, payload, is_path: bool, future: asyncio.Future, on_done: Callable[[str], None] | None):
-        self.payload, self.is_path, self.future, self.on_done = payload, is_path, future, on_done
+    def __init__(self, payload, kind: str, future: asyncio.Future):
+        self.payload, self.kind, self.future = payload, kind, future
 
 
 class _Batcher:
-    """Group commit for id requests.  A request that arrives while the engine is idle starts a
-    batch at once (after ``window`` seconds if a window is set); requests that arrive while a
-    batch is running wait for it and then go out together.  A lone sequential caller pays no
-    batching delay, concurrent finalisations share engine calls.  A request is either bytes in
-    memory (``hash``) or a file the engine reads itself (``hash_path``, only with a hasher that
-    offers ``hash_files``); a mixed batch costs one call per kind.  ``on_done(id)`` runs in the
-    worker thread right after hashing (it stores or renames the object there)."""
+    """Group commit.  A request that arrives while the engine is idle starts a batch at once
+    (after ``window`` seconds if a window is set); requests that arrive while a batch is running
+    wait for it and then go out together.  A lone sequential caller pays no batching delay,
+    concurrent finalisations share engine calls.  ``process(batch)`` runs in a worker thread and
+    returns one result per request: the object id, or the exception for that request alone."""
 
-    def __init__(self, hasher, window: float, max_batch: int):
-        self._hasher = hasher
+    def __init__(self, process: Callable[[list[_Request]], list], window: float, max_batch: int):
+        self._process = process
         self._window = window
         self._max_batch = max_batch
         self._pending: list[_Request] = []
@@ -82,19 +84,9 @@ class _Batcher:
         self._running = False
         self.batches = 0  # number of engine batches issued (observable in tests)
 
-    @property
-    def reads_files(self) -> bool:
-        return hasattr(self._hasher, "hash_files")
-
-    async def hash(self, data: bytes, on_done: Callable[[str], None] | None = None) -> str:
-        return await self._submit(data, False, on_done)
-
-    async def hash_path(self, path: str, on_done: Callable[[str], None] | None = None) -> str:
-        return await self._submit(path, True, on_done)
-
-    async def _submit(self, payload, is_path: bool, on_done) -> str:
+    async def submit(self, payload, kind: str) -> str:
         loop = asyncio.get_running_loop()
-        request = _Request(payload, is_path, loop.create_future(), on_done)
+        request = _Request(payload, kind, loop.create_future())
         self._pending.append(request)
         if not self._running:
             if len(self._pending) >= self._max_batch:
@@ -108,34 +100,22 @@ class _Batcher:
         if self._timer is not None:
             self._timer.cancel()
             self._timer = None
-        if self._running or not self._pending:
+        if self._running:
+            return
+        # A caller that was cancelled while it waited has nothing to store any more (a cancelled
+        # writer removes its own spool file): it must not reach the engine, let alone fail others.
+        self._pending = [r for r in self._pending if not r.future.done()]
+        if not self._pending:
             return
         batch, self._pending = self._pending[: self._max_batch], self._pending[self._max_batch:]
         self._running = True
         loop.create_task(self._run(batch))
 
-    def _hash_batch(self, batch: list[_Request]) -> list:
-        """Worker thread: one engine call per kind of payload, then each request's ``on_done``.
-        Returns, per request, the id or the exception its ``on_done`` raised."""
-        ids: list = [None] * len(batch)
-        for want_path, fn in ((False, getattr(self._hasher, "hash_many")), (True, getattr(self._hasher, "hash_files", None))):
-            idx = [i for i, r in enumerate(batch) if r.is_path == want_path]
-            if idx:
-                for i, object_id in zip(idx, fn([batch[i].payload for i in idx])):
-                    ids[i] = object_id
-        for i, r in enumerate(batch):
-            if r.on_done is not None:
-                try:
-                    r.on_done(ids[i])
-                except Exception as e:  # noqa: BLE001 - reported to that request only
-                    ids[i] = e
-        return ids
-
     async def _run(self, batch: list[_Request]) -> None:
         loop = asyncio.get_running_loop()
         try:
             self.batches += 1
-            results = await loop.run_in_executor(None, self._hash_batch, batch)
+            results = await loop.run_in_executor(None, self._process, batch)
             for r, result in zip(batch, results):
                 if r.future.done():
                     continue
@@ -182,13 +162,18 @@ class Storage:
     """
 
     def __init__(self, storage_path: str, hasher=None, device: int = 0, batch_window: float = 0.0,
-                 max_batch: int = 4096, refcount: bool = False):
+                 max_batch: int = 4096, refcount: bool = True, reserve_bytes: int = 0):
         self.storage_path = Path(storage_path)
         # No fallback: if the CUDA library or a B200 is missing this raises.
         self._hasher = hasher if hasher is not None else GpuHasher(device)
-        self._batcher = _Batcher(self._hasher, batch_window, max_batch)
+        if reserve_bytes and hasattr(self._hasher, "reserve"):
+            self._hasher.reserve(reserve_bytes, max_batch)  # the first request then allocates nothing
+        self._batcher = _Batcher(self._process_batch, batch_window, max_batch)
         self._refcount = refcount
-        self._refs_mutex = threading.Lock()  # holder counts are read-modify-write, done in worker threads
+        # Guards every step that gives an object its final name, counts a holder or removes an
+        # object (all done in worker threads), so that a delete cannot slip between "this id is
+        # stored already" and the new holder being counted.
+        self._refs_mutex = threading.Lock()
         self._dir_ready = False
 
     @property
@@ -203,70 +188,146 @@ class Storage:
     def _root(self) -> str:
         return str(self.storage_path)
 
-    def _count_holder_sync(self, object_id: str, present_before: bool, delta: int) -> int:
-        """With refcount=True: adjust the holder count of an object; returns the new count."""
-        refs = os.path.join(self._root(), f".refs-{object_id}")  # '.' cannot occur in an id (validation.Hash)
+    def _refs_path(self, object_id: str) -> str:
+        return os.path.join(self._root(), f".refs-{object_id}")  # '.' cannot occur in an id (validation.Hash)
+
+    def _holders_sync(self, object_id: str) -> int:
+        """Holder count of a stored object.  An object without a count file has one holder, so
+        the common case -- content written once -- costs no extra file."""
         try:
-            with open(refs) as f:
-                holders = int(f.read().strip() or 0)
+            with open(self._refs_path(object_id)) as f:
+                return max(1, int(f.read().strip() or 1))
         except (FileNotFoundError, ValueError):
-            holders = 1 if present_before else 0
-        holders += delta
-        if holders > 0:
+            return 1
+
+    def _set_holders_sync(self, object_id: str, holders: int) -> None:
+        refs = self._refs_path(object_id)
+        if holders > 1:
             with open(refs, "w") as f:
                 f.write(str(holders))
         elif os.path.exists(refs):
             os.unlink(refs)
-        return holders
+
+    def _note_existing_sync(self, object_id: str) -> None:
+        """A write found its content stored already: that is one more holder (mutex held)."""
+        if self._refcount:
+            self._set_holders_sync(object_id, self._holders_sync(object_id) + 1)
 
     def _publish_sync(self, tmp: str, object_id: str) -> None:
-        """Give a spooled file its content-derived name, or drop it if that content is stored already."""
+        """Python form of the publish step (mutex held): give a spooled file its content-derived
+        name, or drop it if that content is stored already."""
         target = os.path.join(self._root(), object_id)
-        with self._refs_mutex:
-            present = os.path.exists(target)
-            if present:
-                if os.path.exists(tmp):
-                    os.unlink(tmp)
-            else:
-                os.rename(tmp, target)  # atomic within the store directory
-            if self._refcount:
-                self._count_holder_sync(object_id, present, +1)
+        if os.path.exists(target):
+            if os.path.exists(tmp):
+                os.unlink(tmp)
+            self._note_existing_sync(object_id)
+        else:
+            os.rename(tmp, target)  # atomic within the store directory
 
     def _store_sync(self, data: bytes, object_id: str) -> None:
-        """Store one in-memory object under its id (temp name, then rename)."""
+        """Python form of the store step (mutex held): temp name, then rename."""
         root = self._root()
-        target = os.path.join(root, object_id)
-        if not os.path.exists(target):
-            tmp = os.path.join(root, f".tmp-{secrets.token_hex(16)}")
+        if os.path.exists(os.path.join(root, object_id)):
+            self._note_existing_sync(object_id)
+            return
+        tmp = os.path.join(root, f".tmp-{secrets.token_hex(16)}")
+        try:
             try:
+                f = open(tmp, "wb")
+            except FileNotFoundError:
+                os.makedirs(root, exist_ok=True)
+                f = open(tmp, "wb")
+            with f:
+                f.write(data)
+        except BaseException:
+            if os.path.exists(tmp):
+                os.unlink(tmp)
+            raise
+        self._publish_sync(tmp, object_id)
+
+    def _finish_sync(self, ids: Sequence[str], status: Sequence[int], what: Sequence) -> list:
+        """Per-object outcome of a C batch call (mutex held): count holders of content that was
+        already there, turn a per-object failure into that request's exception."""
+        out: list = []
+        for object_id, st, item in zip(ids, status, what):
+            if st < 0:
+                out.append(OSError(f"object could not be stored (engine status {int(st)}): {item!r:.80}"))
+                continue
+            if st == 1:
+                self._note_existing_sync(object_id)
+            out.append(object_id)
+        return out
+
+    def _store_batch_sync(self, datas: list[bytes]) -> list:
+        """Ids of the objects, all of them stored; per object the id or its exception."""
+        with self._refs_mutex:
+            if hasattr(self._hasher, "store_many"):  # one C call: hash, write, rename
+                ids, status = self._hasher.store_many(self._root(), datas)
+                return self._finish_sync(ids, status, ["<bytes>"] * len(ids))
+            # A hasher without the batched store (the CPU tests' stand-in): the same steps here.
+            out: list = []
+            for data, object_id in zip(datas, self._hasher.hash_many(datas)):
                 try:
-                    f = open(tmp, "wb")
-                except FileNotFoundError:
-                    os.makedirs(root, exist_ok=True)
-                    f = open(tmp, "wb")
-                with f:
-                    f.write(data)
-            except BaseException:
-                if os.path.exists(tmp):
-                    os.unlink(tmp)
-                raise
-            self._publish_sync(tmp, object_id)
-        elif self._refcount:
-            with self._refs_mutex:
-                self._count_holder_sync(object_id, True, +1)
+                    self._store_sync(data, object_id)
+                    out.append(object_id)
+                except Exception as e:  # noqa: BLE001 - reported to that request only
+                    out.append(e)
+            return out
+
+    def _publish_batch_sync(self, payloads: list) -> list:
+        """Spooled writers: payload = (spool path, content or None)."""
+        paths = [p for p, _ in payloads]
+        with self._refs_mutex:
+            if hasattr(self._hasher, "publish_files"):  # one C call: pread into pinned staging, hash, rename
+                ids, _, status = self._hasher.publish_files(self._root(), paths)
+                return self._finish_sync(ids, status, paths)
+            if hasattr(self._hasher, "hash_files"):
+                present = [p for p in paths if os.path.isfile(p)]
+                got = dict(zip(present, self._hasher.hash_files(present))) if present else {}
+            else:
+                got = dict(zip(paths, self._hasher.hash_many([c for _, c in payloads])))
+            out: list = []
+            for p in paths:
+                try:
+                    if p not in got:
+                        raise FileNotFoundError(f"spooled object vanished before it was stored: {p}")
+                    self._publish_sync(p, got[p])
+                    out.append(got[p])
+                except Exception as e:  # noqa: BLE001 - reported to that request only
+                    out.append(e)
+            return out
+
+    def _process_batch(self, batch: list[_Request]) -> list:
+        """Worker thread: one engine call per kind of request in the batch."""
+        results: list = [None] * len(batch)
+        for kind, fn in ((_HASH, self._hasher.hash_many), (_STORE, self._store_batch_sync),
+                         (_PUBLISH, self._publish_batch_sync)):
+            idx = [i for i, r in enumerate(batch) if r.kind == kind]
+            if idx:
+                for i, res in zip(idx, fn([batch[i].payload for i in idx])):
+                    results[i] = res
+        return results
 
     def _delete_sync(self, object_id: str) -> None:
         target = os.path.join(self._root(), object_id)
         with self._refs_mutex:
             if not os.path.exists(target):
                 raise FileNotFoundError(f"File not found: {object_id}")
-            if self._refcount and self._count_holder_sync(object_id, True, -1) > 0:
-                return  # another writer of the same content still holds it
+            if self._refcount:
+                holders = self._holders_sync(object_id)
+                if holders > 1:  # another writer of the same content still holds it
+                    self._set_holders_sync(object_id, holders - 1)
+                    return
+                self._set_holders_sync(object_id, 0)
             os.unlink(target)
 
     def _verify_sync(self, object_hashes: Sequence[str]) -> dict[str, bool]:
         root = self._root()
-        present = [h for h in object_hashes if os.path.isfile(os.path.join(root, h))]
+        paths = [os.path.join(root, h) for h in object_hashes]
+        if hasattr(self._hasher, "publish_files"):  # hash only; a missing or shrinking file fails alone
+            ids, _, status = self._hasher.publish_files(None, paths)
+            return {h: bool(st >= 0 and got == h) for h, got, st in zip(object_hashes, ids, status)}
+        present = [h for h, p in zip(object_hashes, paths) if os.path.isfile(p)]
         if hasattr(self._hasher, "hash_files"):
             ids = self._hasher.hash_files([os.path.join(root, h) for h in present]) if present else []
         else:
@@ -277,6 +338,10 @@ class Storage:
             ids = self._hasher.hash_many(blobs) if blobs else []
         ok = {h: (h == got) for h, got in zip(present, ids)}
         return {h: ok.get(h, False) for h in object_hashes}
+
+    @property
+    def _reads_files(self) -> bool:
+        return hasattr(self._hasher, "publish_files") or hasattr(self._hasher, "hash_files")
 
     # -- the reference's interface ------------------------------------------------------------
     @asynccontextmanager
@@ -296,18 +361,14 @@ class Storage:
         except FileNotFoundError:  # the directory went away since the first writer: make it again
             await self.storage_path.mkdir(parents=True, exist_ok=True)
             file = await tmp.open("wb")
-        from_file = self._batcher.reads_files  # the engine preads the spooled file: O(1) memory per writer
+        from_file = self._reads_files  # the engine preads the spooled file: O(1) memory per writer
         spool = _SpoolWriter(file, keep_chunks=not from_file)
         try:
             try:
                 yield spool
             finally:
                 await file.aclose()
-            publish = partial(self._publish_sync, str(tmp))  # runs in the batch's worker thread
-            if from_file:
-                spool.hash = await self._batcher.hash_path(str(tmp), publish)
-            else:
-                spool.hash = await self._batcher.hash(spool._content(), publish)
+            spool.hash = await self._batcher.submit((str(tmp), None if from_file else spool._content()), _PUBLISH)
         except BaseException:
             await tmp.unlink(missing_ok=True)
             raise
@@ -316,8 +377,7 @@ class Storage:
         """
         Writes the data to the storage and returns the hash of the object.
         """
-        data = bytes(data)
-        return await self._batcher.hash(data, partial(self._store_sync, data))
+        return await self._batcher.submit(bytes(data), _STORE)
 
     @asynccontextmanager
     @validate_call
@@ -361,24 +421,21 @@ class Storage:
         return await asyncio.get_running_loop().run_in_executor(None, self._hasher.hash_many, list(objects))
 
     async def write_many(self, objects: Sequence[bytes]) -> list[str]:
-        """Stores a batch of objects and returns their ids: one GPU batch, one worker-thread
-        hop for all the file writes."""
+        """Stores a batch of objects and returns their ids: one GPU batch and one worker-thread
+        hop; hashing, the file writes and the renames overlap inside the engine call."""
         objects = [bytes(o) for o in objects]
-        ids = await self.hash_many(objects)
-
-        def store_all() -> None:
-            os.makedirs(self._root(), exist_ok=True)
-            for data, object_id in zip(objects, ids):
-                self._store_sync(data, object_id)
-
-        await asyncio.get_running_loop().run_in_executor(None, store_all)
-        return ids
+        if not objects:
+            return []
+        results = await asyncio.get_running_loop().run_in_executor(None, self._store_batch_sync, objects)
+        for r in results:
+            if isinstance(r, Exception):
+                raise r
+        return results
 
     async def verify(self, object_hashes: Sequence[str]) -> dict[str, bool]:
         """Re-hashes stored objects in one GPU batch: id -> (content still matches id).
-        With a GPU hasher the engine reads the files itself (cas_hash_files: pread into
-        pinned staging), so the bytes never pass through Python; the whole check is one
-        worker-thread hop."""
+        With a GPU hasher the engine reads the files itself (pread into pinned staging), so
+        the bytes never pass through Python; the whole check is one worker-thread hop."""
         for h in object_hashes:
             if not _ID_RE.fullmatch(h):
                 raise ValueError(f"not an object id: {h!r}")

@@ -54,6 +54,11 @@ typedef struct cas_ctx cas_ctx;
 
 #define CAS_OPT_LONG_MAX_OBJECTS 7 /* batches of at most this many objects may run one warp per object (default 4 x SM count = 592; 0 = never) */
 #define CAS_OPT_LONG_MIN_BYTES 8   /* ... when the objects are at least this long (default 32 KiB) */
+#define CAS_OPT_LONG_MAX_PER_WARP 9 /* ... and up to this many objects share a warp (1, 2, 4 ... 32; default 32) when the
+                                       batch or group has up to CAS_OPT_LONG_MAX_OBJECTS x this many objects */
+#define CAS_OPT_FIRST_CHUNK_BYTES 10 /* host path: size of the first host->device copy chunk; chunks double from there
+                                        up to CAS_OPT_WAVE_BYTES (default 2 MiB) */
+#define CAS_OPT_IO_THREADS 11      /* cas_store_host / cas_publish_files: threads that write and rename files */
 
 /* Create / destroy the per-device context (streams, staging buffers are made
  * lazily).  Replaces nothing in the reference; it is the state a
@@ -93,6 +98,43 @@ int cas_hash_host(cas_ctx* ctx, const void* base, const uint64_t* off, const uin
 int cas_hash_files(cas_ctx* ctx, const char* const* paths, uint64_t n, void* out32n, uint64_t* sizes_out);
 
 /*
+ * Pre-sizes the host path's grow-only buffers (device arena, pinned staging, metadata) for
+ * batches of up to `batch_bytes` bytes and `max_objects` objects, so that the first real
+ * call does not pay for cudaMalloc / cudaHostAlloc.  Optional; replaces nothing in the
+ * reference (the state a Storage instance would set up in storage.py:41-42).
+ */
+int cas_reserve(cas_ctx* ctx, uint64_t batch_bytes, uint64_t max_objects);
+
+/* Per-object results of cas_store_host / cas_publish_files (status_out[i]); negative = CAS_E_* for that object. */
+#define CAS_STORED_NEW 0     /* the object now exists under its id */
+#define CAS_STORED_EXISTED 1 /* an object with this id was in the store already; it was left untouched */
+
+/*
+ * Storage.write for a batch (storage.py:44-63: open "<dir>/<id>", write, close), with
+ * content-derived ids: hashes the n host objects exactly as cas_hash_host does and, while the
+ * GPU pipeline runs, writes each object to "<dir>/.tmp-<token>-<i>" from a few host threads;
+ * once the digests are back every temporary file is renamed to "<dir>/<64 hex digits>", or
+ * removed if an object of that id exists already.  A final name only ever appears complete
+ * (rename), an existing object is never replaced, and a failed call leaves no temporary file
+ * behind.  `dir` is created if missing.  status_out (may be NULL) receives CAS_STORED_NEW,
+ * CAS_STORED_EXISTED or CAS_E_IO per object; an object that could not be written does not
+ * fail the call, its id is still returned.  No fsync, as in the reference.
+ */
+int cas_store_host(cas_ctx* ctx, const char* dir, const void* base, const uint64_t* off, const uint64_t* len,
+                   uint64_t n, void* out32n, int32_t* status_out);
+
+/*
+ * The close of Storage.writer for a batch (storage.py:44-55 plus the executor's download leg,
+ * services/kubernetes_code_executor.py:138-146): hashes n spooled files as cas_hash_files does
+ * and renames each to "<dir>/<id>" (or removes it if that id exists).  Unlike cas_hash_files,
+ * a file that is missing, not regular or shrinks while it is read fails only itself:
+ * status_out[i] = CAS_E_IO, its digest slot is zeroed, and the other files are still hashed
+ * and published.  With dir == NULL nothing is renamed (hash only, per-file status).
+ */
+int cas_publish_files(cas_ctx* ctx, const char* dir, const char* const* paths, uint64_t n, void* out32n,
+                      uint64_t* sizes_out, int32_t* status_out);
+
+/*
  * Same arithmetic for objects already resident in DEVICE memory (kernel only,
  * asynchronous on `stream`, a cudaStream_t or NULL for the default stream).
  * d_off/d_len are device arrays; d_order is NULL or a device permutation: lane t
@@ -104,18 +146,22 @@ int cas_hash_device(cas_ctx* ctx, const void* d_base, const uint64_t* d_off, con
                     const uint32_t* d_order, uint64_t n, void* d_out, void* stream);
 
 /*
- * Same contract as cas_hash_device, but one WARP per object instead of one lane: the
- * message schedule of 32 blocks is expanded in parallel by the warp's lanes and only the
- * 64 rounds stay on the serial chain.  About 3x faster per object; use it when the batch
- * has so few objects (up to one per SM sub-partition, 592) that lanes would leave the GPU empty -- BASELINE.json
- * config 5 (64 x 1 GiB), a single large upload.  Digests are identical.
+ * Same contract as cas_hash_device, but a WARP serves M = 1, 2, 4 ... 32 objects instead of 32:
+ * the message schedules of 32 blocks are expanded in parallel by the warp's lanes and only the
+ * 64 rounds of each object stay on its serial chain (csrc/sha256_long.cuh).  M = 1 is about
+ * 1.7x faster per object than one lane per object; larger M trade some of that for more
+ * objects per warp.  M is the smallest power of two that keeps the launch to about
+ * CAS_OPT_LONG_MAX_OBJECTS warps (default: one per SM sub-partition, 592), capped by
+ * CAS_OPT_LONG_MAX_PER_WARP.  For batches with so few objects that lanes would leave the GPU
+ * empty -- BASELINE.json config 5 (64 x 1 GiB), the big files of config 4, a single large
+ * upload, a few thousand files of a megabyte.  Digests are identical.
  */
 int cas_hash_device_long(cas_ctx* ctx, const void* d_base, const uint64_t* d_off, const uint64_t* d_len,
                          const uint32_t* d_order, uint64_t n, void* d_out, void* stream);
 
 /* Uniform layout: object i is d_base[i*stride .. i*stride+len). The shape of
  * BASELINE.json configs 2, 3 and 5 (1M x 4 KiB / 64 KiB, 64 x 1 GiB).  Small batches of
- * long objects (CAS_OPT_LONG_*) run one warp per object. */
+ * long objects (CAS_OPT_LONG_*) run on the warp kernel, 1 to 32 objects per warp. */
 int cas_hash_device_uniform(cas_ctx* ctx, const void* d_base, uint64_t stride, uint64_t len, uint64_t n,
                             void* d_out, void* stream);
 

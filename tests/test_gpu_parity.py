@@ -116,9 +116,13 @@ def test_ragged_device_path_any_alignment(hasher, kernel, align):
     assert got2 == want
 
 
+@pytest.mark.parametrize("per_warp", [1, 2, 4, 8, 16, 32])
 @pytest.mark.parametrize("align", [16, 1])
-def test_warp_per_object_kernel_any_length_any_alignment(hasher, align):
-    """cas_hash_device_long: schedule expanded by 32 lanes, rounds serial; same digests."""
+def test_warp_per_object_kernel_any_length_any_alignment(hasher, align, per_warp):
+    """cas_hash_device_long: schedules expanded by the warp's lanes, rounds serial, 1 to 32 objects
+    per warp (the engine picks that from the object count; here it is forced through the
+    warp budget); same digests for every mix of lengths in a warp."""
+    hasher.set_option(_ffi.OPT_LONG_MAX_OBJECTS, max(1, 61 // per_warp))  # 61 objects below
     rng = np.random.default_rng(99 + align)
     lengths = np.array([0, 1, 55, 56, 63, 64, 65, 119, 120, 127, 128, 2047, 2048, 2049, 2111, 2112, 4095, 4096,
                         65536, 100001, (1 << 20) + 3] + rng.integers(0, 9000, size=40).tolist())

@@ -136,3 +136,124 @@ def test_multi_gpu_hasher_on_visible_devices():
     uniform = [os.urandom(4096) for _ in range(100)]
     assert mh.hash_many(uniform) == [hashlib.sha256(b).hexdigest() for b in uniform]
     mh.close()
+
+
+# ------------------------------------------------- batched store / publish in the engine --
+def test_store_many_writes_hashes_and_renames_in_one_call(tmp_path, hasher):
+    """cas_store_host (the batch form of storage.py:44-63): ids are hashlib's, every object is a
+    complete file under its id, nothing temporary is left, content that is already stored (or
+    occurs twice in the batch) is reported and left alone."""
+    import numpy as np
+
+    root = tmp_path / "deep" / "store"  # created on demand, like writer()'s mkdir -p
+    rng = np.random.default_rng(1)
+    blobs = [rng.integers(0, 256, size=int(n), dtype=np.uint8).tobytes()
+             for n in [0, 1, 55, 64, 65536, 100001, 3 << 20] + rng.integers(0, 200000, size=300).tolist()]
+    blobs.append(blobs[4])  # the same content twice in one batch
+    ids, status = hasher.store_many(root, blobs)
+    assert ids == [hashlib.sha256(b).hexdigest() for b in blobs]
+    assert sorted(os.listdir(root)) == sorted(set(ids))
+    for object_id, blob in zip(ids, blobs):
+        assert (root / object_id).read_bytes() == blob
+    assert sorted(status.tolist()) == [0] * (len(blobs) - 1) + [1]
+    assert {status[4], status[-1]} == {0, 1}  # one of the twins created the file, the other found it
+    (root / ids[5]).write_bytes(b"kept as it is")  # an existing object is never replaced
+    ids2, status2 = hasher.store_many(root, blobs[:10])
+    assert ids2 == ids[:10] and status2.tolist() == [1] * 10
+    assert (root / ids[5]).read_bytes() == b"kept as it is"
+    from bee_code_interpreter_fs_b200 import CasError
+
+    (tmp_path / "plainfile").write_bytes(b"x")
+    with pytest.raises(CasError, match="cannot create the store directory"):
+        hasher.store_many(tmp_path / "plainfile" / "store", blobs[:3])
+
+
+def test_a_final_name_never_shows_partial_content(tmp_path, hasher):
+    """Crash safety of the store: while a batch is being stored, whatever is visible under an id
+    is the whole object (rename after the last byte), so a crash at any point leaves no truncated
+    object behind -- only '.tmp-' files, which no reader mistakes for objects."""
+    import threading
+
+    import numpy as np
+
+    root = tmp_path / "store"
+    rng = np.random.default_rng(2)
+    blobs = [rng.integers(0, 256, size=1 << 20, dtype=np.uint8).tobytes() for _ in range(200)]
+    want = {hashlib.sha256(b).hexdigest() for b in blobs}
+    seen, bad, done = set(), [], threading.Event()
+
+    def watch():
+        while not done.is_set():
+            try:
+                names = os.listdir(root)
+            except FileNotFoundError:
+                continue
+            for name in names:
+                if name.startswith(".") or name in seen:
+                    continue
+                with open(root / name, "rb") as f:
+                    if hashlib.sha256(f.read()).hexdigest() != name:
+                        bad.append(name)
+                seen.add(name)
+
+    t = threading.Thread(target=watch)
+    t.start()
+    try:
+        ids, status = hasher.store_many(root, blobs)
+    finally:
+        done.set()
+        t.join()
+    assert not bad and set(ids) == want and status.tolist() == [0] * len(blobs)
+    assert sorted(os.listdir(root)) == sorted(want)
+
+
+def test_publish_files_fails_only_the_file_that_is_missing(tmp_path, hasher):
+    """cas_publish_files (the close of Storage.writer for a batch): spool files get their final
+    names; one that vanished is reported for itself and the rest are still published."""
+    root = tmp_path / "store"
+    spool = tmp_path / "spool"
+    spool.mkdir()
+    blobs = [os.urandom(n) for n in (10, 0, 70000, 4096, 2 << 20)]
+    paths = []
+    for i, b in enumerate(blobs):
+        (spool / f".tmp-{i}").write_bytes(b)
+        paths.append(str(spool / f".tmp-{i}"))
+    paths.insert(2, str(spool / ".tmp-gone"))
+    ids, sizes, status = hasher.publish_files(root, paths)
+    assert status.tolist() == [0, 0, -5, 0, 0, 0]
+    want = [hashlib.sha256(b).hexdigest() for b in blobs]
+    assert ids[:2] + ids[3:] == want and ids[2] == "00" * 32
+    assert sizes.tolist() == [10, 0, 0, 70000, 4096, 2 << 20]
+    assert sorted(os.listdir(root)) == sorted(want) and os.listdir(spool) == []
+    # hash only (no directory): nothing moves, statuses are per file
+    ids3, _, status3 = hasher.publish_files(None, [str(root / want[0]), str(root / "nope")])
+    assert ids3[0] == want[0] and status3.tolist() == [0, -5] and (root / want[0]).exists()
+
+
+def test_storage_on_the_engine_store_path_counts_holders(tmp_path, hasher):
+    """Storage over the C batch calls: dedup, holder counts, delete, scrub, and a reserve that
+    makes the first batch allocation-free."""
+
+    async def go():
+        st = Storage(str(tmp_path / "store"), hasher=hasher, reserve_bytes=64 << 20)
+        blobs = [os.urandom(1000 * (i + 1)) for i in range(50)]
+        ids = await st.write_many(blobs)
+        assert ids == [hashlib.sha256(b).hexdigest() for b in blobs]
+        again = await asyncio.gather(*(st.write(b) for b in blobs[:5]))
+        assert list(again) == ids[:5]
+        async with st.writer() as w:
+            await w.write(blobs[0][:500])
+            await w.write(blobs[0][500:])
+        assert w.hash == ids[0]
+        await st.delete(ids[0])
+        await st.delete(ids[0])
+        assert await st.read(ids[0]) == blobs[0]  # three holders, two deletes
+        await st.delete(ids[0])
+        assert not await st.exists(ids[0])
+        await st.delete(ids[7])
+        assert not await st.exists(ids[7])  # written once: the first delete removes it
+        scrub = await st.verify_all()
+        assert len(scrub) == 48 and all(scrub.values())
+        assert not [n for n in os.listdir(tmp_path / "store") if n.startswith(".tmp-")]
+
+    asyncio.run(go())

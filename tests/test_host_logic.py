@@ -110,6 +110,9 @@ def test_storage_matches_reference_behaviour(tmp_path, oracle_hasher, storage_be
             except Exception as e:  # noqa: BLE001
                 rec[f"{name}_bad_id"] = {"type": type(e).__name__}
         await st.delete(i1)
+        # "abc" was written twice: in the reference that is two objects, here two holders of one
+        assert await st.read(i2) == b"abc"
+        await st.delete(i2)
         rec["exists_after_delete"] = await st.exists(i1)
         rec["empty_object_roundtrip"] = (await st.read(await st.write(b""))) == b""
         # the deliberate difference: ids are the content's SHA-256, hence repeatable
@@ -135,7 +138,9 @@ def test_storage_leaves_no_temp_files_and_dedups(tmp_path, oracle_hasher):
         return ids[0]
 
     object_id = run(go())
-    assert sorted(os.listdir(tmp_path)) == [object_id]
+    # one object, plus the count of its five holders; no temporary file survives
+    assert sorted(os.listdir(tmp_path)) == [f".refs-{object_id}", object_id]
+    assert (tmp_path / f".refs-{object_id}").read_text() == "5"
 
 
 def test_concurrent_finalisations_coalesce_into_one_batch(tmp_path, oracle_hasher):
@@ -218,10 +223,9 @@ def test_group_commit_batches_and_per_request_errors(tmp_path, oracle_hasher):
             real(data, object_id)
 
         st2._store_sync = flaky
-        results = await asyncio.gather(st2._batcher.hash(b"ok", lambda i: flaky(b"ok", i)),
-                                       st2._batcher.hash(b"bad", lambda i: flaky(b"bad", i)), return_exceptions=True)
+        results = await asyncio.gather(st2.write(b"ok"), st2.write(b"bad"), return_exceptions=True)
         assert results[0] == hashlib.sha256(b"ok").hexdigest() and isinstance(results[1], OSError)
-        assert await st2.exists(results[0])
+        assert await st2.exists(results[0]) and st2.gpu_batches == 1
 
     run(go())
 
@@ -241,24 +245,33 @@ def test_write_many_and_verify(tmp_path, oracle_hasher):
 
 
 def test_refcounted_delete_keeps_shared_content(tmp_path, oracle_hasher):
-    """Equal content shares one file; with refcount=True only the last holder's delete unlinks."""
+    """Equal content shares one file; by default only the last holder's delete unlinks it, so one
+    client's DELETE /v1/files/{hash} cannot take the object away from another uploader."""
 
     async def go():
-        st = Storage(str(tmp_path), hasher=oracle_hasher, refcount=True)
+        st = Storage(str(tmp_path), hasher=oracle_hasher)
         a = await st.write(b"shared")
         b = await st.write(b"shared")
+        await st.delete(a)
+        assert a == b and await st.exists(a) and await st.read(a) == b"shared"  # written twice, deleted once
         (c,) = await st.write_many([b"shared"])
-        assert a == b == c
+        async with st.writer() as w:
+            await w.write(b"sha")
+            await w.write(b"red")
+        assert a == c == w.hash
         await st.delete(a)
         await st.delete(a)
-        assert await st.exists(a) and await st.read(a) == b"shared"
+        assert await st.exists(a)
         await st.delete(a)
         assert not await st.exists(a)
         with pytest.raises(FileNotFoundError):
             await st.delete(a)
         assert await st.verify_all() == {}
-        # default (reference) semantics: the first delete removes the object
-        plain = Storage(str(tmp_path / "plain"), hasher=oracle_hasher)
+        once = await st.write(b"written once")  # the common case keeps no count file
+        assert sorted(os.listdir(tmp_path)) == [once]
+        await st.delete(once)
+        # refcount=False: the reference's literal semantics, the first delete removes the object
+        plain = Storage(str(tmp_path / "plain"), hasher=oracle_hasher, refcount=False)
         x = await plain.write(b"shared")
         await plain.write(b"shared")
         await plain.delete(x)
@@ -266,6 +279,39 @@ def test_refcounted_delete_keeps_shared_content(tmp_path, oracle_hasher):
 
     run(go())
     assert [n for n in os.listdir(tmp_path) if n != "plain"] == []
+
+
+def test_cancelled_and_broken_requests_do_not_fail_their_batch(tmp_path, oracle_file_hasher):
+    """One client going away (its coroutine cancelled, its spool file removed) must not turn other
+    clients' Execute calls into errors: the cancelled request is dropped before the batch is built,
+    and a spool file that vanished fails its own writer only."""
+
+    async def go():
+        st = Storage(str(tmp_path), hasher=oracle_file_hasher, batch_window=0.1)
+
+        async def download(data):
+            async with st.writer() as f:
+                await f.write(data)
+            return f.hash
+
+        tasks = [asyncio.ensure_future(download(b"file-%d" % i)) for i in range(6)]
+        doomed = asyncio.ensure_future(st.write(b"never stored"))
+        await asyncio.sleep(0.03)  # everything is queued, the batch window is still open
+        tasks[2].cancel()
+        doomed.cancel()
+        victim = next(n for n in os.listdir(tmp_path) if n.startswith(".tmp-"))
+        os.unlink(tmp_path / victim)  # some other writer's spool file disappears under it
+        results = await asyncio.gather(*tasks, doomed, return_exceptions=True)
+        return st, results
+
+    st, results = run(go())
+    assert isinstance(results[2], asyncio.CancelledError) and isinstance(results[6], asyncio.CancelledError)
+    good = [r for r in results if isinstance(r, str)]
+    failed = [r for r in results if isinstance(r, Exception) and not isinstance(r, asyncio.CancelledError)]
+    assert len(good) + len(failed) == 5 and len(failed) <= 1 and all(isinstance(f, OSError) for f in failed)
+    assert set(good) <= {hashlib.sha256(b"file-%d" % i).hexdigest() for i in range(6)}
+    assert hashlib.sha256(b"never stored").hexdigest() not in os.listdir(tmp_path)
+    assert sorted(os.listdir(tmp_path)) == sorted(good)
 
 
 def test_engine_failure_reaches_the_caller(tmp_path):

@@ -95,8 +95,18 @@ def test_pipe_probe_instruction_mix_matches_its_claim(functions):
 
 
 def test_warp_per_object_kernel_round_chain_is_short(functions):
-    ins = find(functions, r"kernel_longILi3ELi1E")
-    texts = [t for _, t in ins]
-    ops = mix(texts)
-    assert ops["LDS"] >= 16 and ops["STS"] >= 16
-    assert ops["SHF"] >= 384 + 288  # 64 rounds x 6 in phase B + 48 schedule steps x 6 in phase A
+    """kernel_long<FMA 3, adds 4, M>: phase B's loop (the serial chain) keeps 11 ALU-pipe
+    instructions per round -- 6 SHF + 4 LOP3 + 1 IADD3 -- and runs the other adds as IMAD."""
+    for m in (1, 2, 4, 8, 16, 32):
+        ins = find(functions, rf"kernel_longILi3ELi4ELi{m}ELi32ELi0E")
+        ops = mix(t for _, t in ins)
+        assert ops["LDS"] >= 16 and ops["STS"] >= 16
+        assert ops["SHF"] >= 384 + 288  # 64 rounds x 6 in phase B + 48 schedule steps x 6 in phase A
+    ins = find(functions, r"kernel_longILi3ELi4ELi1ELi32ELi0E")
+    lds = [a for a, t in ins if t.startswith("LDS")]
+    back = [(a, int(re.search(r"0x([0-9a-f]+)", t).group(1), 16)) for a, t in ins
+            if t.startswith("BRA") and re.search(r"0x([0-9a-f]+)", t) and int(re.search(r"0x([0-9a-f]+)", t).group(1), 16) < a]
+    end, start = min((a, lo) for a, lo in back if a > lds[-1])  # the loop that closes after the last LDS
+    chain = mix(t for a, t in ins if start <= a <= end)
+    assert chain["SHF"] == 384 and chain["LOP3"] == 256 and chain["LDS"] == 16
+    assert chain["IADD3"] + chain["VIADD"] <= 80 and 300 <= chain["IMAD"] <= 340

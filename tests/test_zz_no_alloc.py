@@ -80,33 +80,34 @@ def test_static_entry_point_rejects_what_does_not_fit():
     assert (got == _hashlib_digests(edge)).all()
 
 
-def test_static_entry_point_recovers_after_a_call_that_failed_half_way():
-    """A call that fails after it has queued work must wait that work out before it gives the
-    shared array up, and must leave the calling thread's device alone.  Here the output pointer
-    is device memory, which the final device-to-host copy refuses -- after the object copies and
-    the kernel are already on the stream.  The next call has to succeed and be exact."""
+def test_static_entry_point_rejections_leave_it_usable_and_the_device_alone():
+    """Rejected calls (NULL arrays, a NULL object address) must not disturb the next call, and the
+    calling thread's current device must be what it was.  (The drain-before-return on a CUDA error
+    after work was queued cannot be provoked from outside on a healthy one-GPU box -- a device
+    pointer as output is accepted by the runtime under unified addressing -- so it is covered by
+    reading csrc/engine.cu, not by this test.)"""
     import torch
 
     lib = _ffi.load()
     objs = _batch(3, 500, 6000)
     n = len(objs)
-    ptrs = (ctypes.c_char_p * n)(*objs)
-    off = np.frombuffer(ptrs, dtype=np.uint64, count=n).copy()
     length = np.fromiter(map(len, objs), dtype=np.uint64, count=n)
-    bad_out = torch.zeros(n * 32, dtype=torch.uint8, device="cuda:0")
-    torch.cuda.synchronize()
+    out = np.zeros((n, 32), dtype=np.uint8)
     before = torch.cuda.current_device()
-    rc = lib.cas_hash_host_static(0, None, off.ctypes.data, length.ctypes.data, n, bad_out.data_ptr(), None)
-    assert rc == _ffi.CAS_E_CUDA and b"digest copy" in lib.cas_last_error(None)
-    assert torch.cuda.current_device() == before
-    rc = lib.cas_hash_host_static(0, None, None, length.ctypes.data, n, bad_out.data_ptr(), None)
+    rc = lib.cas_hash_host_static(0, None, None, length.ctypes.data, n, out.ctypes.data, None)
     assert rc == _ffi.CAS_E_ARG
     null_src = np.zeros(1, dtype=np.uint64)
     one_len = np.ones(1, dtype=np.uint64)
-    out = np.zeros((1, 32), dtype=np.uint8)
     rc = lib.cas_hash_host_static(0, None, null_src.ctypes.data, one_len.ctypes.data, 1, out.ctypes.data, None)
     assert rc == _ffi.CAS_E_ARG and b"NULL address" in lib.cas_last_error(None)
-    # straight after the failures: a different batch over the stale bytes, exact
+    rc = lib.cas_hash_host_static(4096, None, null_src.ctypes.data, one_len.ctypes.data, 1, out.ctypes.data, None)
+    assert rc == _ffi.CAS_E_ARG
+    if torch.cuda.device_count() > 1:  # the call runs on device 1 and hands device 0 back
+        rc, got = _static_digests(lib, objs, device=1)
+        assert rc == _ffi.CAS_OK, lib.cas_last_error(None)
+        assert (got == _hashlib_digests(objs)).all()
+    assert torch.cuda.current_device() == before
+    # straight after the rejections: a different batch over the stale bytes, exact
     again = _batch(4, 400, 5000)
     rc, got = _static_digests(lib, again)
     assert rc == _ffi.CAS_OK, lib.cas_last_error(None)
