@@ -8,7 +8,7 @@ import subprocess
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG_DIR, "csrc")
 LIB_PATH = os.path.join(PKG_DIR, "libb200cas.so")
-SOURCES = ["engine.cu"]
+SOURCES = ["engine.cu", "hostcopy.cpp"]
 HEADERS = sorted(f for f in os.listdir(CSRC) if f.endswith((".cuh", ".h")))  # every header engine.cu may include
 NVCC_FLAGS = [
     "-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",

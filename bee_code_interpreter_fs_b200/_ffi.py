@@ -17,7 +17,7 @@ STORED_NEW, STORED_EXISTED = 0, 1
 SYMBOLS = (
     "cas_create", "cas_destroy", "cas_last_error", "cas_set_option", "cas_get_option", "cas_device_info",
     "cas_hash_host", "cas_hash_files", "cas_hash_device", "cas_hash_device_long", "cas_hash_device_uniform", "cas_gen_synthetic", "cas_int32_peak",
-    "cas_launch_count", "cas_version", "cas_hash_host_static", "cas_reserve", "cas_store_host", "cas_publish_files",
+    "cas_launch_count", "cas_version", "cas_hash_host_static", "cas_reserve", "cas_store_host", "cas_publish_files", "cas_verify_names",
 )
 STATIC_MAX_OBJECTS = 1024
 STATIC_MAX_BYTES = 8 << 20
@@ -79,6 +79,8 @@ def load() -> ctypes.CDLL:
     lib.cas_store_host.restype = ci
     lib.cas_publish_files.argtypes = [vp, ctypes.c_char_p, vp, u64, vp, vp, vp]
     lib.cas_publish_files.restype = ci
+    lib.cas_verify_names.argtypes = [vp, ctypes.c_char_p, ctypes.c_char_p, u64, vp]
+    lib.cas_verify_names.restype = ci
     lib.cas_launch_count.argtypes = [vp]
     lib.cas_launch_count.restype = u64
     lib.cas_version.argtypes = []

@@ -36,6 +36,7 @@
 #include <vector>
 
 #include "../../include/b200cas.h"
+#include "hostcopy.h"
 #include "peak.cuh"
 #include "sha256_batch.cuh"
 #include "sha256_long.cuh"
@@ -342,14 +343,26 @@ void free_host_path(cas_ctx* c) {
         if (ev) { cudaEventDestroy(ev); ev = nullptr; }
 }
 
+// The pool serves two kinds of work: packing host memory into pinned staging (memory-bound:
+// half the cores, at most 8, measured best on a 16-core host -- 50 vs 42 GB/s with 16) and
+// reading files into it (syscall-bound: every core helps).  It is sized for the larger.
+int pack_width(const cas_ctx* ctx) {
+    if (ctx->pack_threads > 0) return ctx->pack_threads;
+    return std::max(1, std::min((int)std::thread::hardware_concurrency() / 2, 8));
+}
+
+int file_width(const cas_ctx* ctx) {
+    if (ctx->io_threads > 0) return ctx->io_threads;
+    return std::max(1, std::min((int)std::thread::hardware_concurrency(), 32));
+}
+
 void ensure_pack_pool(cas_ctx* ctx) {
-    if (ctx->pool) return;
-    int n = ctx->pack_threads;
-    if (n <= 0) {  // half the cores, at most 8: measured best on a 16-core host (50 vs 42 GB/s with 16)
-        n = (int)std::thread::hardware_concurrency() / 2;
-        n = std::max(1, std::min(n, 8));
+    const int want = std::max(pack_width(ctx), file_width(ctx));
+    if (ctx->pool && ctx->pool->size() != want) {
+        delete ctx->pool;
+        ctx->pool = nullptr;
     }
-    ctx->pool = new PackPool(n);
+    if (!ctx->pool) ctx->pool = new PackPool(want);
 }
 
 // Grow-only resources of the host path: nothing is allocated per call once the
@@ -503,10 +516,6 @@ int cas_set_option(cas_ctx* ctx, int key, int64_t v) {
             return CAS_OK;
         case CAS_OPT_PACK_THREADS:
             if (v < 1 || v > 256) return fail(ctx, CAS_E_ARG, "CAS_OPT_PACK_THREADS must be 1..256");
-            if (ctx->pool && ctx->pool->size() != (int)v) {
-                delete ctx->pool;
-                ctx->pool = nullptr;
-            }
             ctx->pack_threads = (int)v;
             return CAS_OK;
         case CAS_OPT_ARENA_BYTES:
@@ -536,10 +545,6 @@ int cas_set_option(cas_ctx* ctx, int key, int64_t v) {
             return CAS_OK;
         case CAS_OPT_IO_THREADS:
             if (v < 1 || v > 256) return fail(ctx, CAS_E_ARG, "CAS_OPT_IO_THREADS must be 1..256");
-            if (ctx->io_pool && ctx->io_pool->size() != (int)v) {
-                delete ctx->io_pool;
-                ctx->io_pool = nullptr;
-            }
             ctx->io_threads = (int)v;
             return CAS_OK;
     }
@@ -552,14 +557,14 @@ int cas_get_option(const cas_ctx* ctx, int key, int64_t* v) {
         case CAS_OPT_KERNEL: *v = ctx->kernel; return CAS_OK;
         case CAS_OPT_FMA_LEVEL: *v = ctx->fma_level; return CAS_OK;
         case CAS_OPT_WAVE_BYTES: *v = (int64_t)ctx->wave_bytes; return CAS_OK;
-        case CAS_OPT_PACK_THREADS: *v = ctx->pool ? ctx->pool->size() : ctx->pack_threads; return CAS_OK;
+        case CAS_OPT_PACK_THREADS: *v = pack_width(ctx); return CAS_OK;
         case CAS_OPT_CTAS_PER_SM: *v = ctx->ctas_per_sm; return CAS_OK;
         case CAS_OPT_ARENA_BYTES: *v = (int64_t)ctx->arena_max; return CAS_OK;
         case CAS_OPT_LONG_MAX_OBJECTS: *v = (int64_t)ctx->long_max_objects; return CAS_OK;
         case CAS_OPT_LONG_MIN_BYTES: *v = (int64_t)ctx->long_min_bytes; return CAS_OK;
         case CAS_OPT_LONG_MAX_PER_WARP: *v = ctx->long_max_m; return CAS_OK;
         case CAS_OPT_FIRST_CHUNK_BYTES: *v = (int64_t)ctx->first_chunk; return CAS_OK;
-        case CAS_OPT_IO_THREADS: *v = ctx->io_pool ? ctx->io_pool->size() : ctx->io_threads; return CAS_OK;
+        case CAS_OPT_IO_THREADS: *v = file_width(ctx); return CAS_OK;
     }
     return CAS_E_ARG;
 }
@@ -714,10 +719,12 @@ bool read_file_range(const char* path, uint64_t offset, uint8_t* dst, uint64_t b
 
 // ------------------------------------------------------------------ store-side file helpers --
 void ensure_io_pool(cas_ctx* ctx) {
-    if (ctx->io_pool) return;
-    int n = ctx->io_threads;
-    if (n <= 0) n = std::max(1, std::min((int)std::thread::hardware_concurrency() / 2, 8));
-    ctx->io_pool = new PackPool(n);
+    const int want = file_width(ctx);
+    if (ctx->io_pool && ctx->io_pool->size() != want) {
+        delete ctx->io_pool;
+        ctx->io_pool = nullptr;
+    }
+    if (!ctx->io_pool) ctx->io_pool = new PackPool(want);
 }
 
 // mkdir -p
@@ -746,10 +753,19 @@ uint64_t fresh_token() {
     return t ^ ((uint64_t)getpid() << 40) ^ ((uint64_t)tv.tv_usec << 20) ^ (uint64_t)tv.tv_sec ^ (counter.fetch_add(1) << 56);
 }
 
-// Temporary names start with '.', which no object id can (the reference's Hash pattern,
-// utils/validation.py:19), so a reader can never mistake a half-written file for an object.
-void tmp_name(char* dst, size_t cap, uint64_t token, uint64_t i) {
-    snprintf(dst, cap, ".tmp-%016llx-%llu", (unsigned long long)token, (unsigned long long)i);
+// Temporary files live in per-writer-thread directories "<dir>/.tmp-<token>.<t>/": creating a
+// file takes its parent directory's lock, and with one directory per thread the writers do
+// not queue on it (nor on the store directory, which then only sees the final renames).
+// The names start with '.', which no object id can (the reference's Hash pattern,
+// utils/validation.py:19), so a reader can never mistake anything in there for an object.
+void tmp_dir_name(char* dst, size_t cap, uint64_t token, unsigned writer) {
+    snprintf(dst, cap, ".tmp-%016llx.%u", (unsigned long long)token, writer);
+}
+
+std::string tmp_path(const std::string& root, uint64_t token, unsigned writer, uint64_t i) {
+    char name[96];
+    snprintf(name, sizeof name, "/.tmp-%016llx.%u/%llu", (unsigned long long)token, writer, (unsigned long long)i);
+    return root + name;
 }
 
 bool write_whole_file(const char* path, const uint8_t* src, uint64_t bytes) {
@@ -791,47 +807,49 @@ int rename_noreplace(const char* tmp, const char* target) {
     return err == EEXIST ? CAS_STORED_EXISTED : CAS_E_IO;
 }
 
-// Final names for a batch: tmp files made by cas_store_host (paths == NULL: names from the
-// token) or the caller's spool files.  Objects whose status is already negative are skipped
-// (their tmp file is removed if it is ours).
-void publish_tmp_files(cas_ctx* ctx, const std::string& root, uint64_t token, const char* const* paths, uint64_t n,
-                       const uint8_t* digests, int32_t* status) {
+// Final names for a batch: tmp files made by cas_store_host (paths == NULL: writer[i] says
+// which thread's directory holds object i) or the caller's spool files.  Objects whose status
+// is already negative are skipped (their tmp file is removed if it is ours).
+void publish_tmp_files(cas_ctx* ctx, const std::string& root, uint64_t token, const uint16_t* writer,
+                       const char* const* paths, uint64_t n, const uint8_t* digests, int32_t* status) {
     std::atomic<uint64_t> next{0};
     const std::function<void(int)> job = [&](int) {
-        char name[64], hex[65];
+        char hex[65];
         for (;;) {
-            const uint64_t i = next.fetch_add(1, std::memory_order_relaxed);
-            if (i >= n) return;
-            std::string tmp;
-            if (paths) {
-                tmp = paths[i];
-            } else {
-                tmp_name(name, sizeof name, token, i);
-                tmp = root + "/" + name;
+            const uint64_t i0 = next.fetch_add(16, std::memory_order_relaxed);
+            if (i0 >= n) return;
+            for (uint64_t i = i0; i < std::min(n, i0 + 16); ++i) {
+                const std::string tmp = paths ? std::string(paths[i]) : tmp_path(root, token, writer[i], i);
+                if (status[i] < 0) {
+                    if (!paths) unlink(tmp.c_str());
+                    continue;
+                }
+                hex_name(hex, digests + 32 * i);
+                status[i] = rename_noreplace(tmp.c_str(), (root + "/" + hex).c_str());
             }
-            if (status[i] < 0) {
-                if (!paths) unlink(tmp.c_str());
-                continue;
-            }
-            hex_name(hex, digests + 32 * i);
-            status[i] = rename_noreplace(tmp.c_str(), (root + "/" + hex).c_str());
         }
     };
     ctx->io_pool->run(job);
 }
 
-void remove_tmp_files(cas_ctx* ctx, const std::string& root, uint64_t token, uint64_t n) {
-    std::atomic<uint64_t> next{0};
-    const std::function<void(int)> job = [&](int) {
-        char name[64];
-        for (;;) {
-            const uint64_t i = next.fetch_add(1, std::memory_order_relaxed);
-            if (i >= n) return;
-            tmp_name(name, sizeof name, token, i);
-            unlink((root + "/" + name).c_str());
-        }
-    };
-    ctx->io_pool->run(job);
+// Removes what is left of a store call's temporary directories (all of it after a failed call).
+void remove_tmp_dirs(cas_ctx* ctx, const std::string& root, uint64_t token, const uint16_t* writer, uint64_t n, bool files_too) {
+    if (files_too) {
+        std::atomic<uint64_t> next{0};
+        const std::function<void(int)> job = [&](int) {
+            for (;;) {
+                const uint64_t i = next.fetch_add(1, std::memory_order_relaxed);
+                if (i >= n) return;
+                if (writer[i] != 0xFFFF) unlink(tmp_path(root, token, writer[i], i).c_str());
+            }
+        };
+        ctx->io_pool->run(job);
+    }
+    char name[64];
+    for (int t = 0; t < ctx->io_pool->size(); ++t) {
+        tmp_dir_name(name, sizeof name, token, (unsigned)t);
+        rmdir((root + "/" + name).c_str());  // absent if that thread wrote nothing
+    }
 }
 
 // Sizes of n files, looked up by the pack pool's threads.  With status == NULL a file that is
@@ -990,12 +1008,13 @@ int hash_host_impl(cas_ctx* ctx, const ByteSource& srcs, const uint64_t* len, ui
                     const double tw0 = ctx->trace ? now_s() : 0.0;
                     if (sg.used) CU(cudaEventSynchronize(sg.ev));  // its previous H2D has left the staging
                     const double tw1 = ctx->trace ? now_s() : 0.0;
-                    const int T = ctx->pool->size();
+                    const int T = std::min(ctx->pool->size(), from_files ? file_width(ctx) : pack_width(ctx));
                     const uint64_t span = c1 - c0, share = ((span + T - 1) / (uint64_t)T + 63) & ~63ull;
                     uint8_t* stage = sg.h;
                     const Piece* pv = pieces.data();
                     const size_t np = pieces.size();
                     ctx->pool->run([&](int t) {
+                        if (t >= T) return;
                         const uint64_t lo = c0 + share * (uint64_t)t, hi = std::min(c1, lo + share);
                         if (lo >= hi) return;
                         // first piece that ends after lo
@@ -1003,7 +1022,7 @@ int hash_host_impl(cas_ctx* ctx, const ByteSource& srcs, const uint64_t* len, ui
                         for (; i < np && pv[i].dst < hi; ++i) {
                             const uint64_t a = std::max(pv[i].dst, lo), b = std::min(pv[i].dst + pv[i].bytes, hi);
                             if (pv[i].src) {
-                                memcpy(stage + (a - c0), pv[i].src + (a - pv[i].dst), b - a);
+                                cas::copy_to_staging(stage + (a - c0), pv[i].src + (a - pv[i].dst), b - a);
                             } else if (status && status[pv[i].obj] < 0) {
                                 memset(stage + (a - c0), 0, b - a);  // already failed: keep the staging defined
                             } else if (!read_file_range(srcs.paths[pv[i].obj], pv[i].fpos + (a - pv[i].dst), stage + (a - c0), b - a)) {
@@ -1146,14 +1165,21 @@ int cas_store_host(cas_ctx* ctx, const char* dir, const void* base, const uint64
     const uint64_t token = fresh_token();
 
     // File writers run while this thread drives the GPU pipeline over the same bytes.
+    std::vector<uint16_t> writer(n, 0xFFFF);
     std::atomic<uint64_t> next{0};
-    const std::function<void(int)> write_all = [&](int) {
+    const std::function<void(int)> write_all = [&](int t) {
+        bool have_dir = false;
         char name[64];
         for (;;) {
             const uint64_t i = next.fetch_add(1, std::memory_order_relaxed);
             if (i >= n) return;
-            tmp_name(name, sizeof name, token, i);
-            if (!write_whole_file((root + "/" + name).c_str(), hbase + off[i], len[i])) status[i] = CAS_E_IO;
+            if (!have_dir) {
+                tmp_dir_name(name, sizeof name, token, (unsigned)t);
+                have_dir = mkdir((root + "/" + name).c_str(), 0777) == 0 || errno == EEXIST;
+            }
+            writer[i] = (uint16_t)t;
+            if (!have_dir || !write_whole_file(tmp_path(root, token, (unsigned)t, i).c_str(), hbase + off[i], len[i]))
+                status[i] = CAS_E_IO;
         }
     };
     ctx->io_pool->start(write_all);
@@ -1163,10 +1189,11 @@ int cas_store_host(cas_ctx* ctx, const char* dir, const void* base, const uint64
     const int rc = hash_host_impl(ctx, src, len, n, static_cast<uint8_t*>(out32n));
     ctx->io_pool->wait();
     if (rc) {  // no ids: nothing may appear under a final name
-        remove_tmp_files(ctx, root, token, n);
+        remove_tmp_dirs(ctx, root, token, writer.data(), n, true);
         return rc;
     }
-    publish_tmp_files(ctx, root, token, nullptr, n, static_cast<const uint8_t*>(out32n), status);
+    publish_tmp_files(ctx, root, token, writer.data(), nullptr, n, static_cast<const uint8_t*>(out32n), status);
+    remove_tmp_dirs(ctx, root, token, writer.data(), n, false);
     return CAS_OK;
 }
 
@@ -1191,7 +1218,59 @@ int cas_publish_files(cas_ctx* ctx, const char* dir, const char* const* paths, u
     uint8_t* out = static_cast<uint8_t*>(out32n);
     for (uint64_t i = 0; i < n; ++i)
         if (status_out[i] < 0) memset(out + 32 * i, 0, 32);  // never a digest of bytes that were not all read
-    if (dir) publish_tmp_files(ctx, std::string(dir), 0, paths, n, out, status_out);
+    if (dir) publish_tmp_files(ctx, std::string(dir), 0, nullptr, paths, n, out, status_out);
+    return CAS_OK;
+}
+
+int cas_verify_names(cas_ctx* ctx, const char* dir, const char* names, uint64_t n, uint8_t* result_out) {
+    if (!ctx) return CAS_E_ARG;
+    if (n == 0) return CAS_OK;
+    if (!dir || !names || !result_out) return fail(ctx, CAS_E_ARG, "cas_verify_names: NULL directory, names or result array");
+    if (n > 0xFFFFFFFFull) return fail(ctx, CAS_E_ARG, "cas_verify_names: more than 2^32-1 names in one call");
+    CU(cudaSetDevice(ctx->device));
+    const std::string root(dir);
+    std::vector<const char*> name(n);
+    std::vector<std::string> path(n);
+    std::vector<const char*> cpath(n);
+    const char* p = names;
+    for (uint64_t i = 0; i < n; ++i) {
+        name[i] = p;
+        path[i] = root + "/" + p;
+        cpath[i] = path[i].c_str();
+        p += strlen(p) + 1;
+    }
+    std::vector<uint64_t> len(n);
+    std::vector<int32_t> status(n, 0);
+    int rc = stat_files(ctx, cpath.data(), n, len.data(), status.data());
+    if (rc) return rc;
+    // Only what can be an object is read: a regular file with a 64-character name.
+    std::vector<uint32_t> pick;
+    for (uint64_t i = 0; i < n; ++i) {
+        if (status[i] < 0) {
+            struct stat sb;
+            result_out[i] = (stat(cpath[i], &sb) == 0 && !S_ISREG(sb.st_mode)) ? CAS_VERIFY_NOT_A_FILE : CAS_VERIFY_BAD;
+        } else if (strlen(name[i]) != 64) {
+            result_out[i] = CAS_VERIFY_BAD;  // cannot be the hex form of a SHA-256 digest
+        } else {
+            pick.push_back((uint32_t)i);
+        }
+    }
+    const uint64_t m = pick.size();
+    if (m == 0) return CAS_OK;
+    std::vector<const char*> ppath(m);
+    std::vector<uint64_t> plen(m);
+    std::vector<int32_t> pstatus(m, 0);
+    std::vector<uint8_t> dig(m * 32);
+    for (uint64_t k = 0; k < m; ++k) { ppath[k] = cpath[pick[k]]; plen[k] = len[pick[k]]; }
+    ByteSource src;
+    src.paths = ppath.data();
+    rc = hash_host_impl(ctx, src, plen.data(), m, dig.data(), pstatus.data());
+    if (rc) return rc;
+    char hex[65];
+    for (uint64_t k = 0; k < m; ++k) {
+        hex_name(hex, dig.data() + 32 * k);
+        result_out[pick[k]] = (pstatus[k] >= 0 && memcmp(hex, name[pick[k]], 64) == 0) ? CAS_VERIFY_OK : CAS_VERIFY_BAD;
+    }
     return CAS_OK;
 }
 

@@ -14,21 +14,60 @@ def env_world() -> tuple[int, int, int]:
     return (int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)))
 
 
+_ORDER_FILE = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "profiles", "h2d_gpu_order.json")
+
+
+def gpu_order(device_count: int) -> list[int]:
+    """The order in which the GPUs of this node are handed to ranks (and to MultiGpuHasher).
+
+    Objects are independent, so ranks never talk to each other and any GPU serves any rank; what
+    differs between GPUs is the host uplink they hang off.  With N < all GPUs in use, taking them
+    in an order measured to spread over distinct uplinks (tools/h2d_matrix.cu, "greedy" section,
+    kept in profiles/h2d_gpu_order.json) gives the N concurrent host->device streams more of the
+    host's bandwidth than GPUs 0..N-1 would.  ``B200CAS_GPU_ORDER=0,4,1,5,...`` overrides it; a
+    map measured on a node with a different GPU count is ignored (identity order)."""
+    order = None
+    env = os.environ.get("B200CAS_GPU_ORDER")
+    try:
+        if env:
+            order = [int(x) for x in env.split(",") if x.strip()]
+        else:
+            import json
+
+            with open(_ORDER_FILE) as f:
+                order = [int(x) for x in json.load(f)["order"]]
+    except (OSError, ValueError, KeyError):
+        order = None
+    if not order or sorted(order) != list(range(device_count)):
+        return list(range(device_count))
+    return order
+
+
+def gpu_for_rank(local_rank: int, device_count: int) -> int:
+    order = gpu_order(device_count)
+    return order[local_rank] if local_rank < len(order) else local_rank
+
+
 def init(backend: str | None = None) -> tuple[int, int, int]:
+    """Rendezvous.  Returns (rank, device index for this rank, world size); the device index is
+    ``gpu_for_rank(local_rank)`` with the nccl backend and the local rank otherwise."""
     import torch
     import torch.distributed as dist
 
     rank, local_rank, world = env_world()
+    device = local_rank
+    if torch.cuda.is_available():
+        device = gpu_for_rank(local_rank, torch.cuda.device_count())
     if world > 1 and not dist.is_initialized():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         os.environ.setdefault("MASTER_PORT", "29531")
         backend = backend or ("nccl" if torch.cuda.is_available() else "gloo")
         if backend == "nccl":
-            torch.cuda.set_device(local_rank)
-            dist.init_process_group(backend, device_id=torch.device("cuda", local_rank))
+            torch.cuda.set_device(device)
+            dist.init_process_group(backend, device_id=torch.device("cuda", device))
         else:
             dist.init_process_group(backend)
-    return rank, local_rank, world
+    return rank, device, world
 
 
 def _device():

@@ -25,15 +25,37 @@ def hex_ids(digests: np.ndarray) -> list[str]:
     return [flat[i:i + 64] for i in range(0, len(flat), 64)]
 
 
+def _bytes_data_offset() -> int:
+    """Offset of a ``bytes`` object's characters from ``id(obj)`` on this interpreter, or 0 if it
+    cannot be confirmed (then addresses are taken one by one through ctypes).  Saves about
+    0.3 us per object on the way into the engine, which matters for batches of small objects."""
+    try:
+        guess = bytes.__basicsize__ - 1
+        for probe in (b"probe-one", b"x" * 5000, b""):
+            want = ctypes.cast(ctypes.c_char_p(probe), ctypes.c_void_p).value
+            if id(probe) + guess != want:
+                return 0
+        return guess
+    except Exception:  # noqa: BLE001 - not CPython, or a layout this check does not know
+        return 0
+
+
+_BYTES_DATA_OFFSET = _bytes_data_offset()
+
+
 def _addresses(objs: Sequence[BytesLike]) -> tuple[np.ndarray, np.ndarray, list]:
     """Host addresses and lengths of the objects, without copying them."""
     n = len(objs)
     keep: list = []
     if set(map(type, objs)) <= {bytes}:
         length = np.fromiter(map(len, objs), dtype=np.uint64, count=n)
-        arr = (ctypes.c_char_p * n)(*objs)  # pointers into the bytes objects themselves
-        addr = np.frombuffer(arr, dtype=np.uint64, count=n).copy() if n else np.zeros(0, np.uint64)
-        keep.append(arr)
+        if _BYTES_DATA_OFFSET:  # CPython: the characters sit at a fixed offset inside the object
+            addr = np.fromiter(map(id, objs), dtype=np.uint64, count=n) + np.uint64(_BYTES_DATA_OFFSET)
+            keep.append(objs)
+        else:
+            arr = (ctypes.c_char_p * n)(*objs)  # pointers into the bytes objects themselves
+            addr = np.frombuffer(arr, dtype=np.uint64, count=n).copy() if n else np.zeros(0, np.uint64)
+            keep.append(arr)
     else:
         length = np.fromiter((len(o) if not isinstance(o, np.ndarray) else o.nbytes for o in objs), dtype=np.uint64,
                              count=n)
@@ -263,6 +285,19 @@ class GpuHasher:
         with self._lock:
             self._check(self._lib.cas_int32_peak(self._ctx, int(mode), int(steps), ctypes.byref(ops), ctypes.byref(ms)))
         return ops.value, ms.value
+
+
+    def verify_names(self, root: str | os.PathLike, names: Sequence[str]) -> np.ndarray:
+        """Scrub: per name 1 if sha256(<root>/<name>) spells the name, 0 if not (or unreadable),
+        2 if the entry is not a regular file (cas_verify_names)."""
+        n = len(names)
+        out = np.zeros(n, dtype=np.uint8)
+        if n == 0:
+            return out
+        blob = "\0".join(names).encode() + b"\0"
+        with self._lock:
+            self._check(self._lib.cas_verify_names(self._ctx, os.fsencode(root), blob, n, out.ctypes.data))
+        return out
 
 
 class MultiGpuHasher:

@@ -323,11 +323,10 @@ class Storage:
 
     def _verify_sync(self, object_hashes: Sequence[str]) -> dict[str, bool]:
         root = self._root()
-        paths = [os.path.join(root, h) for h in object_hashes]
-        if hasattr(self._hasher, "publish_files"):  # hash only; a missing or shrinking file fails alone
-            ids, _, status = self._hasher.publish_files(None, paths)
-            return {h: bool(st >= 0 and got == h) for h, got, st in zip(object_hashes, ids, status)}
-        present = [h for h, p in zip(object_hashes, paths) if os.path.isfile(p)]
+        if hasattr(self._hasher, "verify_names"):  # read, hashed and compared inside the engine call
+            ok = self._hasher.verify_names(root, object_hashes)
+            return dict(zip(object_hashes, (ok == 1).tolist()))
+        present = [h for h in object_hashes if os.path.isfile(os.path.join(root, h))]
         if hasattr(self._hasher, "hash_files"):
             ids = self._hasher.hash_files([os.path.join(root, h) for h in present]) if present else []
         else:
@@ -448,6 +447,10 @@ class Storage:
             root = self._root()
             if not os.path.isdir(root):
                 return {}
+            if hasattr(self._hasher, "verify_names"):  # the engine tells files from other entries itself
+                names = sorted(n for n in os.listdir(root) if not n.startswith("."))
+                ok = self._hasher.verify_names(root, names)
+                return {n: bool(v == 1) for n, v in zip(names, ok.tolist()) if v != 2}
             names = sorted(e.name for e in os.scandir(root) if not e.name.startswith(".") and e.is_file())
             return self._verify_sync(names)
 

@@ -112,9 +112,9 @@ int cas_reserve(cas_ctx* ctx, uint64_t batch_bytes, uint64_t max_objects);
 /*
  * Storage.write for a batch (storage.py:44-63: open "<dir>/<id>", write, close), with
  * content-derived ids: hashes the n host objects exactly as cas_hash_host does and, while the
- * GPU pipeline runs, writes each object to "<dir>/.tmp-<token>-<i>" from a few host threads;
- * once the digests are back every temporary file is renamed to "<dir>/<64 hex digits>", or
- * removed if an object of that id exists already.  A final name only ever appears complete
+ * GPU pipeline runs, writes each object to a temporary file under "<dir>/.tmp-<token>.<thread>/"
+ * from a few host threads; once the digests are back every temporary file is renamed to
+ * "<dir>/<64 hex digits>", or removed if an object of that id exists already.  A final name only ever appears complete
  * (rename), an existing object is never replaced, and a failed call leaves no temporary file
  * behind.  `dir` is created if missing.  status_out (may be NULL) receives CAS_STORED_NEW,
  * CAS_STORED_EXISTED or CAS_E_IO per object; an object that could not be written does not
@@ -133,6 +133,20 @@ int cas_store_host(cas_ctx* ctx, const char* dir, const void* base, const uint64
  */
 int cas_publish_files(cas_ctx* ctx, const char* dir, const char* const* paths, uint64_t n, void* out32n,
                       uint64_t* sizes_out, int32_t* status_out);
+
+/*
+ * Integrity scrub of stored objects: the reference names a file by its id (storage.py:53), so
+ * an object is intact when the SHA-256 of "<dir>/<name>" spells <name>.  `names` holds n
+ * NUL-terminated names back to back; result_out[i] receives CAS_VERIFY_OK, CAS_VERIFY_BAD
+ * (content does not match the name, the file is missing, unreadable or shrank while it was
+ * read, or the name is not 64 characters) or CAS_VERIFY_NOT_A_FILE (a directory or other
+ * non-regular entry, which a scrub of a whole directory should skip).  Files are read by the
+ * host threads straight into pinned staging, as in cas_hash_files.
+ */
+#define CAS_VERIFY_BAD 0
+#define CAS_VERIFY_OK 1
+#define CAS_VERIFY_NOT_A_FILE 2
+int cas_verify_names(cas_ctx* ctx, const char* dir, const char* names, uint64_t n, uint8_t* result_out);
 
 /*
  * Same arithmetic for objects already resident in DEVICE memory (kernel only,

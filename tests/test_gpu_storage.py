@@ -257,3 +257,25 @@ def test_storage_on_the_engine_store_path_counts_holders(tmp_path, hasher):
         assert not [n for n in os.listdir(tmp_path / "store") if n.startswith(".tmp-")]
 
     asyncio.run(go())
+
+
+def test_scrub_in_the_engine_tells_objects_from_everything_else(tmp_path, hasher):
+    """cas_verify_names: per name ok / bad / not a file; Storage.verify_all skips what cannot be
+    an object (sub-directories, dot files) and flags what is wrong under an id."""
+    root = tmp_path / "store"
+    blobs = [os.urandom(n) for n in (0, 1, 4096, 65536, 300001)]
+    ids, _ = hasher.store_many(root, blobs)
+    (root / "subdir").mkdir()
+    (root / ".refs-something").write_text("2")
+    (root / ("a" * 64)).write_bytes(b"not what the name says")
+    (root / "short-name").write_bytes(b"x")
+    got = hasher.verify_names(root, ids + ["subdir", "a" * 64, "short-name", "f" * 64])
+    assert got.tolist() == [1] * 5 + [2, 0, 0, 0]
+
+    async def go():
+        st = Storage(str(root), hasher=hasher)
+        scrub = await st.verify_all()
+        assert scrub == {**{i: True for i in ids}, "a" * 64: False, "short-name": False}
+        assert await st.verify(ids[:2] + ["0" * 64]) == {ids[0]: True, ids[1]: True, "0" * 64: False}
+
+    asyncio.run(go())
