@@ -12,6 +12,10 @@
                           utils/validation}.py: which ids/paths validate, the
                           id shape, the error types and messages.
 
+* grpc_wire.json       -- the Execute messages as the reference's generated protobuf
+                          descriptor declares them (numbers, types, map patterns from the
+                          buf.validate options) and sample wire bytes from its classes.
+
 /root/reference does not exist on the GPU box, hence fixtures.
 """
 from __future__ import annotations
@@ -137,7 +141,42 @@ def storage_behaviour() -> dict:
     return out
 
 
+def grpc_wire() -> dict:
+    """Facts about the Execute messages, read from the reference's generated descriptor
+    (submodules/bee-proto/gen/python): field numbers and types, the two map patterns taken from
+    the buf.validate options, the service path, and the bytes the reference's classes produce
+    for one request and one response (so that a wire-compatible restatement can be checked
+    where the reference is absent)."""
+    sys.path.insert(0, "/root/reference/submodules/bee-proto/gen/python")
+    import proto.code_interpreter.v1.code_interpreter_service_pb2 as pb
+    from buf.validate import validate_pb2
+
+    def fields(msg):
+        return [{"name": f.name, "number": f.number, "type": f.type, "label": f.label,
+                 "map_entry": bool(f.message_type and f.message_type.GetOptions().map_entry)} for f in msg.DESCRIPTOR.fields]
+
+    def patterns(msg):
+        rules = msg.DESCRIPTOR.fields_by_name["files"].GetOptions().Extensions[validate_pb2.field].map
+        return {"keys": rules.keys.string.pattern, "values": rules.values.string.pattern}
+
+    files = {"/workspace/file.txt": hashlib.sha256(b"Hello, World!").hexdigest(), "/workspace/b": "A-b_9"}
+    req = pb.ExecuteRequest(source_code="print('hi')", files=files)
+    resp = pb.ExecuteResponse(stdout="hi\n", stderr="", exit_code=3, files=files)
+    svc = pb.DESCRIPTOR.services_by_name["CodeInterpreterService"]
+    return {"package": pb.DESCRIPTOR.package, "service": svc.full_name,
+            "execute_method": {"name": "Execute", "input": svc.methods_by_name["Execute"].input_type.full_name,
+                               "output": svc.methods_by_name["Execute"].output_type.full_name},
+            "ExecuteRequest": {"fields": fields(pb.ExecuteRequest), "files_patterns": patterns(pb.ExecuteRequest)},
+            "ExecuteResponse": {"fields": fields(pb.ExecuteResponse), "files_patterns": patterns(pb.ExecuteResponse)},
+            "sample": {"files": files, "request_source_code": "print('hi')",
+                       "request_hex": req.SerializeToString(deterministic=True).hex(),
+                       "response": {"stdout": "hi\n", "stderr": "", "exit_code": 3},
+                       "response_hex": resp.SerializeToString(deterministic=True).hex()}}
+
+
 if __name__ == "__main__":
+    with open(os.path.join(HERE, "grpc_wire.json"), "w") as f:
+        json.dump(grpc_wire(), f, indent=1)
     with open(os.path.join(HERE, "sha256_kat.json"), "w") as f:
         json.dump(kat(), f, indent=1)
     with open(os.path.join(HERE, "storage_behaviour.json"), "w") as f:
