@@ -1274,6 +1274,165 @@ int cas_verify_names(cas_ctx* ctx, const char* dir, const char* names, uint64_t 
     return CAS_OK;
 }
 
+}  // extern "C"
+
+namespace {
+
+// Copies `bytes` of the virtual input "a followed by b" starting at `pos` to dst.
+void gather2(uint8_t* dst, const uint8_t* a, uint64_t alen, const uint8_t* b, uint64_t pos, uint64_t bytes) {
+    if (pos < alen) {
+        const uint64_t k = std::min(bytes, alen - pos);
+        memcpy(dst, a + pos, k);
+        dst += k; pos += k; bytes -= k;
+    }
+    if (bytes) cas::copy_to_staging(dst, b + (pos - alen), bytes);
+}
+
+// Advances n chains over whole 64-byte blocks.  The input of stream i is a[i] (alen[i] bytes)
+// followed by b[i] (blen[i] bytes), alen + blen a multiple of 64.  Goes in rounds of at most one
+// staging buffer; a stream's blocks may be split between rounds (that is what the state is for).
+int stream_blocks(cas_ctx* ctx, cas_stream_state* const* s, const uint8_t* const* a, const uint64_t* alen,
+                  const uint8_t* const* b, const uint64_t* blen, uint64_t n) {
+    if (ctx->host_path_dirty) CU(cudaDeviceSynchronize());
+    const uint64_t round_cap = std::max<uint64_t>(MiB, std::min<uint64_t>(ctx->wave_bytes, 256 * MiB)) & ~63ull;
+    int rc = ensure_host_path(ctx, round_cap, round_cap, n);
+    if (rc) return rc;
+    ctx->host_path_dirty = true;
+    std::vector<uint64_t> done(n, 0);  // bytes of each stream's input already hashed
+    uint64_t first = 0;                // first stream that still has blocks
+    struct Entry { uint64_t stream, stage_off, bytes; };
+    std::vector<Entry> entries;
+    cudaStream_t st = ctx->s_comp[0];
+    for (;;) {
+        while (first < n && done[first] == alen[first] + blen[first]) ++first;
+        if (first >= n) break;
+        entries.clear();
+        uint64_t used = 0;
+        for (uint64_t i = first; i < n && used < round_cap; ++i) {
+            const uint64_t left = alen[i] + blen[i] - done[i];
+            if (!left) continue;
+            const uint64_t take = std::min(left, round_cap - used);
+            entries.push_back({i, used, take});
+            used += take;
+        }
+        const uint64_t m = entries.size();
+        uint8_t* stage = ctx->stage[0].h;
+        uint64_t* h_off = ctx->h_meta;
+        uint64_t* h_nblk = ctx->h_meta + m;
+        uint32_t* h_state = reinterpret_cast<uint32_t*>(ctx->h_dig);
+        const Entry* ev = entries.data();
+        ctx->pool->run([&](int t) {
+            const int T = ctx->pool->size();
+            for (uint64_t k = (uint64_t)t; k < m; k += (uint64_t)T) {
+                const Entry& e = ev[k];
+                gather2(stage + e.stage_off, a[e.stream], alen[e.stream], b[e.stream], done[e.stream], e.bytes);
+            }
+        });
+        for (uint64_t k = 0; k < m; ++k) {
+            h_off[k] = entries[k].stage_off;
+            h_nblk[k] = entries[k].bytes / 64;
+            memcpy(h_state + 8 * k, s[entries[k].stream]->h, 32);
+        }
+        CU(cudaMemcpyAsync(ctx->d_arena, stage, used, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(ctx->d_meta, h_off, m * 16, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(ctx->d_dig, h_state, m * 32, cudaMemcpyHostToDevice, st));
+        cas::kernel_resume<3, 32><<<(unsigned)((m + 31) / 32), 32, 0, st>>>(
+            ctx->d_arena, ctx->d_meta, ctx->d_meta + m, reinterpret_cast<uint32_t*>(ctx->d_dig), m, 1u);
+        CU(cudaGetLastError());
+        ++ctx->launches;
+        CU(cudaMemcpyAsync(h_state, ctx->d_dig, m * 32, cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        for (uint64_t k = 0; k < m; ++k) {
+            memcpy(s[entries[k].stream]->h, h_state + 8 * k, 32);
+            done[entries[k].stream] += entries[k].bytes;
+        }
+    }
+    ctx->host_path_dirty = false;
+    return CAS_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+void cas_stream_begin(cas_stream_state* s) {
+    if (!s) return;
+    static const uint32_t iv[8] = {0x6a09e667u, 0xbb67ae85u, 0x3c6ef372u, 0xa54ff53au,
+                                   0x510e527fu, 0x9b05688cu, 0x1f83d9abu, 0x5be0cd19u};  // FIPS 180-4 section 5.3.3
+    memcpy(s->h, iv, sizeof iv);
+    s->length = 0;
+    memset(s->tail, 0, sizeof s->tail);
+}
+
+int cas_stream_update(cas_ctx* ctx, cas_stream_state* const* streams, const void* const* data, const uint64_t* len,
+                      uint64_t n) {
+    if (!ctx) return CAS_E_ARG;
+    if (n == 0) return CAS_OK;
+    if (!streams || !data || !len) return fail(ctx, CAS_E_ARG, "cas_stream_update: NULL stream, data or length array");
+    CU(cudaSetDevice(ctx->device));
+    std::vector<const uint8_t*> a(n), b(n);
+    std::vector<uint64_t> alen(n), blen(n);
+    for (uint64_t i = 0; i < n; ++i) {
+        if (!streams[i] || (len[i] && !data[i])) return fail(ctx, CAS_E_ARG, "cas_stream_update: NULL stream or data pointer");
+        const uint64_t have = streams[i]->length & 63u;
+        const uint64_t whole = (have + len[i]) & ~63ull;  // bytes that make whole blocks
+        a[i] = streams[i]->tail;
+        b[i] = static_cast<const uint8_t*>(data[i]);
+        alen[i] = whole ? have : 0;
+        blen[i] = whole ? whole - have : 0;
+    }
+    const int rc = stream_blocks(ctx, streams, a.data(), alen.data(), b.data(), blen.data(), n);
+    if (rc) return rc;  // states may be part-way through this update: the streams are no longer usable
+    for (uint64_t i = 0; i < n; ++i) {
+        const uint64_t have = streams[i]->length & 63u;
+        const uint8_t* src = static_cast<const uint8_t*>(data[i]);
+        if (alen[i] + blen[i]) {  // the old tail was consumed; what is left of data becomes the new tail
+            const uint64_t rest = len[i] - blen[i];
+            memcpy(streams[i]->tail, src + blen[i], rest);
+        } else {
+            memcpy(streams[i]->tail + have, src, len[i]);
+        }
+        streams[i]->length += len[i];
+    }
+    return CAS_OK;
+}
+
+int cas_stream_finish(cas_ctx* ctx, cas_stream_state* const* streams, uint64_t n, void* out32n) {
+    if (!ctx) return CAS_E_ARG;
+    if (n == 0) return CAS_OK;
+    if (!streams || !out32n) return fail(ctx, CAS_E_ARG, "cas_stream_finish: NULL stream or output array");
+    CU(cudaSetDevice(ctx->device));
+    // FIPS 180-4 section 5.1.1: 0x80, zeros, the bit length as a 64-bit big-endian number.
+    std::vector<uint8_t> pad(n * 128, 0);
+    std::vector<const uint8_t*> a(n), b(n);
+    std::vector<uint64_t> alen(n), blen(n, 0);
+    for (uint64_t i = 0; i < n; ++i) {
+        if (!streams[i]) return fail(ctx, CAS_E_ARG, "cas_stream_finish: NULL stream");
+        const uint64_t have = streams[i]->length & 63u;
+        uint8_t* p = pad.data() + 128 * i;
+        memcpy(p, streams[i]->tail, have);
+        p[have] = 0x80;
+        const uint64_t total = have + 9 <= 64 ? 64 : 128;
+        const uint64_t bits = streams[i]->length << 3;
+        for (int k = 0; k < 8; ++k) p[total - 1 - k] = (uint8_t)(bits >> (8 * k));
+        a[i] = p;
+        alen[i] = total;
+        b[i] = nullptr;
+    }
+    const int rc = stream_blocks(ctx, streams, a.data(), alen.data(), b.data(), blen.data(), n);
+    if (rc) return rc;
+    uint8_t* out = static_cast<uint8_t*>(out32n);
+    for (uint64_t i = 0; i < n; ++i)
+        for (int w = 0; w < 8; ++w) {
+            const uint32_t v = streams[i]->h[w];
+            out[32 * i + 4 * w + 0] = (uint8_t)(v >> 24);
+            out[32 * i + 4 * w + 1] = (uint8_t)(v >> 16);
+            out[32 * i + 4 * w + 2] = (uint8_t)(v >> 8);
+            out[32 * i + 4 * w + 3] = (uint8_t)v;
+        }
+    return CAS_OK;
+}
+
 // ---------------------------------------------------------------------------
 // cas_hash_host_static: the host-buffer path for callers that must not allocate.
 //

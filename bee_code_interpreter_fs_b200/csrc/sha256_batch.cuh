@@ -168,6 +168,41 @@ __global__ void __launch_bounds__(THREADS, MIN_CTAS) kernel_ldg(const BatchArgs 
     store_digest(A.out + idx * 32u, st);
 }
 
+// -------------------------------------------------------------- kernel_resume --
+// Streaming form: lane t continues the chain of stream t from the 8-word state it is given
+// over `nblk[t]` whole 64-byte blocks at base + off[t] (16-byte aligned) and writes the state
+// back.  No padding here: the caller appends the FIPS 180-4 tail as ordinary blocks when the
+// stream ends (cas_stream_finish).  States are host-order 32-bit words, 8 per stream.
+template <int FMA_LEVEL, int THREADS>
+__global__ void __launch_bounds__(THREADS) kernel_resume(const uint8_t* __restrict__ base, const uint64_t* __restrict__ off,
+                                                         const uint64_t* __restrict__ nblk, uint32_t* __restrict__ state,
+                                                         uint64_t n, uint32_t one) {
+    const uint64_t t = (uint64_t)blockIdx.x * THREADS + threadIdx.x;
+    if (t >= n) return;
+    const uint64_t nb = nblk[t];
+    if (nb == 0) return;
+    const uint8_t* p = base + off[t];
+    uint32_t st[8];
+    const uint4 s0 = reinterpret_cast<const uint4*>(state + 8 * t)[0], s1 = reinterpret_cast<const uint4*>(state + 8 * t)[1];
+    st[0] = s0.x; st[1] = s0.y; st[2] = s0.z; st[3] = s0.w; st[4] = s1.x; st[5] = s1.y; st[6] = s1.z; st[7] = s1.w;
+    uint4 q0 = ldg_nc_v4(p), q1 = ldg_nc_v4(p + 16), q2 = ldg_nc_v4(p + 32), q3 = ldg_nc_v4(p + 48);
+#pragma unroll 1
+    for (uint64_t i = 0; i < nb; ++i) {
+        uint32_t w[16];
+        w[0] = bswap32(q0.x); w[1] = bswap32(q0.y); w[2] = bswap32(q0.z); w[3] = bswap32(q0.w);
+        w[4] = bswap32(q1.x); w[5] = bswap32(q1.y); w[6] = bswap32(q1.z); w[7] = bswap32(q1.w);
+        w[8] = bswap32(q2.x); w[9] = bswap32(q2.y); w[10] = bswap32(q2.z); w[11] = bswap32(q2.w);
+        w[12] = bswap32(q3.x); w[13] = bswap32(q3.y); w[14] = bswap32(q3.z); w[15] = bswap32(q3.w);
+        if (i + 1 < nb) {
+            const uint8_t* pn = p + ((i + 1) << 6);
+            q0 = ldg_nc_v4(pn); q1 = ldg_nc_v4(pn + 16); q2 = ldg_nc_v4(pn + 32); q3 = ldg_nc_v4(pn + 48);
+        }
+        sha256_compress<FMA_LEVEL>(st, w, one);
+    }
+    reinterpret_cast<uint4*>(state + 8 * t)[0] = make_uint4(st[0], st[1], st[2], st[3]);
+    reinterpret_cast<uint4*>(state + 8 * t)[1] = make_uint4(st[4], st[5], st[6], st[7]);
+}
+
 // --------------------------------------------------------------- kernel_bulk --
 // Shared-memory plan per warp: NSTAGE stages, each 32 slots of SLOT_PITCH bytes
 // (64 data bytes + 16 pad so that the 8 lanes of an LDS.128 phase hit 8

@@ -287,6 +287,37 @@ class GpuHasher:
         return ops.value, ms.value
 
 
+    # -- objects that arrive in pieces ---------------------------------------------------------
+    def stream_begin(self) -> "_ffi.StreamState":
+        """A fresh streaming state (plain data: it can be kept, copied or dropped freely)."""
+        st = _ffi.StreamState()
+        self._lib.cas_stream_begin(ctypes.byref(st))
+        return st
+
+    def stream_update(self, states: Sequence["_ffi.StreamState"], pieces: Sequence[BytesLike]) -> None:
+        """Feeds one piece to each stream; all streams advance in one GPU launch (cas_stream_update)."""
+        n = len(states)
+        if n != len(pieces):
+            raise ValueError("one piece per stream")
+        if n == 0:
+            return
+        addr, length, keep = _addresses(pieces)
+        ptrs = (ctypes.c_void_p * n)(*[ctypes.addressof(s) for s in states])
+        with self._lock:
+            self._check(self._lib.cas_stream_update(self._ctx, ptrs, addr.ctypes.data, length.ctypes.data, n))
+        del keep
+
+    def stream_finish(self, states: Sequence["_ffi.StreamState"]) -> list[str]:
+        """Pads and closes the streams; returns their ids.  The states must not be used again."""
+        n = len(states)
+        if n == 0:
+            return []
+        out = np.empty((n, 32), dtype=np.uint8)
+        ptrs = (ctypes.c_void_p * n)(*[ctypes.addressof(s) for s in states])
+        with self._lock:
+            self._check(self._lib.cas_stream_finish(self._ctx, ptrs, n, out.ctypes.data))
+        return hex_ids(out)
+
     def verify_names(self, root: str | os.PathLike, names: Sequence[str]) -> np.ndarray:
         """Scrub: per name 1 if sha256(<root>/<name>) spells the name, 0 if not (or unreadable),
         2 if the entry is not a regular file (cas_verify_names)."""

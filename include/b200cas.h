@@ -149,6 +149,30 @@ int cas_publish_files(cas_ctx* ctx, const char* dir, const char* const* paths, u
 int cas_verify_names(cas_ctx* ctx, const char* dir, const char* names, uint64_t n, uint8_t* result_out);
 
 /*
+ * Streaming form: objects that arrive in pieces -- what the reference's writers do, chunk by
+ * chunk (storage.py:44-55; the executor's download leg feeds `stored_file.write(chunk)`,
+ * services/kubernetes_code_executor.py:139-145) -- or that are larger than device memory.
+ * The running state of a stream is plain data owned by the caller: the 8 chaining words, the
+ * byte count and the up to 63 bytes that do not fill a block yet.  cas_stream_update takes n
+ * streams and one piece of host memory for each, runs all whole 64-byte blocks through the GPU
+ * from each stream's own state (one launch for the n chains; pieces larger than the staging
+ * buffer go in rounds, which is the same thing as more updates) and keeps the remainder in the
+ * state.  cas_stream_finish appends the FIPS 180-4 padding as ordinary blocks, runs them on
+ * the GPU too, and writes the n digests.  The same stream must not be in two calls at once.
+ * The throughput path for whole objects is cas_hash_host; this one pays a device round trip per
+ * update and exists for correctness with unbounded inputs, not for speed.
+ */
+typedef struct cas_stream_state {
+    uint32_t h[8];     /* chaining value, host byte order */
+    uint64_t length;   /* bytes absorbed so far */
+    uint8_t tail[64];  /* the last length % 64 bytes, not yet compressed */
+} cas_stream_state;
+void cas_stream_begin(cas_stream_state* s); /* the FIPS 180-4 initial hash value, length 0 */
+int cas_stream_update(cas_ctx* ctx, cas_stream_state* const* streams, const void* const* data, const uint64_t* len,
+                      uint64_t n);
+int cas_stream_finish(cas_ctx* ctx, cas_stream_state* const* streams, uint64_t n, void* out32n);
+
+/*
  * Same arithmetic for objects already resident in DEVICE memory (kernel only,
  * asynchronous on `stream`, a cudaStream_t or NULL for the default stream).
  * d_off/d_len are device arrays; d_order is NULL or a device permutation: lane t

@@ -29,4 +29,3 @@ run_bench() {  # $1 = ranks, $2 = tag, $3 = order ("" = identity)
 run_bench 8 ordered "$ORDER"
 run_bench 4 ordered "$ORDER"
 run_bench 4 identity "0,1,2,3,4,5,6,7"
-run_bench 2 ordered "$ORDER"
