@@ -10,7 +10,7 @@ CAS_OK = 0
 CAS_E_CUDA, CAS_E_ARG, CAS_E_NOMEM, CAS_E_NODEVICE, CAS_E_IO = -1, -2, -3, -4, -5
 OPT_KERNEL, OPT_FMA_LEVEL, OPT_WAVE_BYTES, OPT_PACK_THREADS, OPT_CTAS_PER_SM, OPT_ARENA_BYTES = 1, 2, 3, 4, 5, 6
 OPT_LONG_MAX_OBJECTS, OPT_LONG_MIN_BYTES = 7, 8
-OPT_LONG_MAX_PER_WARP, OPT_FIRST_CHUNK_BYTES, OPT_IO_THREADS = 9, 10, 11
+OPT_LONG_MAX_PER_WARP, OPT_FIRST_CHUNK_BYTES, OPT_IO_THREADS, OPT_CHUNK_DIVISOR = 9, 10, 11, 12
 STORED_NEW, STORED_EXISTED = 0, 1
 
 # Every symbol include/b200cas.h declares (tests check the library exports them all).

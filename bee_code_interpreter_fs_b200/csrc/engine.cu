@@ -141,6 +141,7 @@ struct cas_ctx {
     uint64_t long_min_bytes = 32768;   // ... if the objects are at least this long
     int long_max_m = 32;               // groups of up to long_max_objects x this many long objects run M objects per warp
     uint64_t first_chunk = 2 * MiB;    // host path: size of the first copy chunk (chunks double up to the cap)
+    uint64_t chunk_div = 8;            // host path: a batch is cut into at least about this many chunks
     cudaStream_t s_copy = nullptr;
     cudaStream_t s_comp[NCOMP] = {};
     cudaEvent_t ev_epoch[2][NCOMP] = {};  // kernels of the epoch that last used an arena half
@@ -543,6 +544,10 @@ int cas_set_option(cas_ctx* ctx, int key, int64_t v) {
             if (v < 65536) return fail(ctx, CAS_E_ARG, "CAS_OPT_FIRST_CHUNK_BYTES must be >= 64 KiB");
             ctx->first_chunk = ((uint64_t)v + 65535) & ~65535ull;
             return CAS_OK;
+        case CAS_OPT_CHUNK_DIVISOR:
+            if (v < 1 || v > 1024) return fail(ctx, CAS_E_ARG, "CAS_OPT_CHUNK_DIVISOR must be 1..1024");
+            ctx->chunk_div = (uint64_t)v;
+            return CAS_OK;
         case CAS_OPT_IO_THREADS:
             if (v < 1 || v > 256) return fail(ctx, CAS_E_ARG, "CAS_OPT_IO_THREADS must be 1..256");
             ctx->io_threads = (int)v;
@@ -565,6 +570,7 @@ int cas_get_option(const cas_ctx* ctx, int key, int64_t* v) {
         case CAS_OPT_LONG_MAX_PER_WARP: *v = ctx->long_max_m; return CAS_OK;
         case CAS_OPT_FIRST_CHUNK_BYTES: *v = (int64_t)ctx->first_chunk; return CAS_OK;
         case CAS_OPT_IO_THREADS: *v = file_width(ctx); return CAS_OK;
+        case CAS_OPT_CHUNK_DIVISOR: *v = (int64_t)ctx->chunk_div; return CAS_OK;
     }
     return CAS_E_ARG;
 }
@@ -932,7 +938,7 @@ int hash_host_impl(cas_ctx* ctx, const ByteSource& srcs, const uint64_t* len, ui
     // keeps at least ~8 of them in a batch (copy and hash overlap) and at most wave_bytes.
     // The arena has two halves so that the copies of one epoch run while the kernels of
     // the previous one finish.
-    const uint64_t chunk_cap = std::min<uint64_t>(ctx->wave_bytes, std::max<uint64_t>(8 * MiB, (total / 8 + MiB - 1) & ~(MiB - 1)));
+    const uint64_t chunk_cap = std::min<uint64_t>(ctx->wave_bytes, std::max<uint64_t>(8 * MiB, (total / ctx->chunk_div + MiB - 1) & ~(MiB - 1)));
     uint64_t chunk_now = std::min<uint64_t>(chunk_cap, ctx->first_chunk);
     uint64_t half = std::max<uint64_t>(std::min<uint64_t>(ctx->arena_max / 2, (total + MiB - 1) & ~(MiB - 1)),
                                        std::max<uint64_t>(align16(maxlen), 16));
@@ -940,7 +946,19 @@ int hash_host_impl(cas_ctx* ctx, const ByteSource& srcs, const uint64_t* len, ui
     const bool one_epoch = total <= half;
     int rc = ensure_host_path(ctx, one_epoch ? half : 2 * half, chunk_cap, n);
     if (rc) return rc;
-    const bool pinned_src = !from_files && host_ptr_is_pinned(hbase);
+    // Page-locked source memory is DMA'd straight from where it lies.  With absolute addresses
+    // (hbase == NULL) the first, middle and last object stand for the batch; should other
+    // objects be pageable after all, their copies still work, only slower.
+    bool pinned_src = false;
+    if (!from_files) {
+        if (hbase) {
+            pinned_src = host_ptr_is_pinned(hbase);
+        } else if (total >= 8 * MiB) {
+            pinned_src = true;
+            for (uint64_t k : {uint64_t(0), n / 2, n - 1})
+                pinned_src = pinned_src && (len[k] == 0 || host_ptr_is_pinned(reinterpret_cast<const void*>(off[k])));
+        }
+    }
 
     // Device layout in schedule order; epochs are runs of objects that fit one arena half.
     uint64_t* h_off = ctx->h_meta;
@@ -1141,7 +1159,7 @@ int cas_reserve(cas_ctx* ctx, uint64_t batch_bytes, uint64_t max_objects) {
     CU(cudaSetDevice(ctx->device));
     if (ctx->host_path_dirty) CU(cudaDeviceSynchronize());
     const uint64_t total = std::max<uint64_t>(batch_bytes, MiB);
-    const uint64_t chunk_cap = std::min<uint64_t>(ctx->wave_bytes, std::max<uint64_t>(8 * MiB, (total / 8 + MiB - 1) & ~(MiB - 1)));
+    const uint64_t chunk_cap = std::min<uint64_t>(ctx->wave_bytes, std::max<uint64_t>(8 * MiB, (total / ctx->chunk_div + MiB - 1) & ~(MiB - 1)));
     uint64_t half = std::min<uint64_t>(ctx->arena_max / 2, (total + MiB - 1) & ~(MiB - 1));
     half = (half + 255) & ~255ull;
     return ensure_host_path(ctx, total <= half ? half : 2 * half, chunk_cap, std::max<uint64_t>(max_objects, 1));

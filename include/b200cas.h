@@ -58,7 +58,9 @@ typedef struct cas_ctx cas_ctx;
                                        batch or group has up to CAS_OPT_LONG_MAX_OBJECTS x this many objects */
 #define CAS_OPT_FIRST_CHUNK_BYTES 10 /* host path: size of the first host->device copy chunk; chunks double from there
                                         up to CAS_OPT_WAVE_BYTES (default 2 MiB) */
-#define CAS_OPT_IO_THREADS 11      /* cas_store_host / cas_publish_files: threads that write and rename files */
+#define CAS_OPT_IO_THREADS 11      /* threads that read, write and rename files (cas_hash_files, cas_store_host,
+                                      cas_publish_files, cas_verify_names); default: every core, at most 32 */
+#define CAS_OPT_CHUNK_DIVISOR 12   /* host path: a batch is cut into at least about this many copy chunks (default 8) */
 
 /* Create / destroy the per-device context (streams, staging buffers are made
  * lazily).  Replaces nothing in the reference; it is the state a
