@@ -141,7 +141,7 @@ struct cas_ctx {
     uint64_t long_min_bytes = 32768;   // ... if the objects are at least this long
     int long_max_m = 32;               // groups of up to long_max_objects x this many long objects run M objects per warp
     uint64_t first_chunk = 2 * MiB;    // host path: size of the first copy chunk (chunks double up to the cap)
-    uint64_t chunk_div = 8;            // host path: a batch is cut into at least about this many chunks
+    uint64_t chunk_div = 16;           // host path: a batch is cut into at least about this many chunks
     cudaStream_t s_copy = nullptr;
     cudaStream_t s_comp[NCOMP] = {};
     cudaEvent_t ev_epoch[2][NCOMP] = {};  // kernels of the epoch that last used an arena half
@@ -344,17 +344,18 @@ void free_host_path(cas_ctx* c) {
         if (ev) { cudaEventDestroy(ev); ev = nullptr; }
 }
 
-// The pool serves two kinds of work: packing host memory into pinned staging (memory-bound:
-// half the cores, at most 8, measured best on a 16-core host -- 50 vs 42 GB/s with 16) and
-// reading files into it (syscall-bound: every core helps).  It is sized for the larger.
+// The pool serves two kinds of work: packing host memory into pinned staging (memory-bound)
+// and reading files into it (syscall-bound).  Both did best with three quarters of a 16-vCPU
+// host's threads (profiles/r02_host_sweep.jsonl: 12 pack threads 16.6 ms vs 18.0 with 8 and
+// 17.3 with 16 for 10 000 x 64 KiB; file reads 23 ms with 12, 27 with 8, 25 with 16).
 int pack_width(const cas_ctx* ctx) {
     if (ctx->pack_threads > 0) return ctx->pack_threads;
-    return std::max(1, std::min((int)std::thread::hardware_concurrency() / 2, 8));
+    return std::max(1, std::min((int)std::thread::hardware_concurrency() * 3 / 4, 12));
 }
 
 int file_width(const cas_ctx* ctx) {
     if (ctx->io_threads > 0) return ctx->io_threads;
-    return std::max(1, std::min((int)std::thread::hardware_concurrency(), 32));
+    return std::max(1, std::min((int)std::thread::hardware_concurrency() * 3 / 4, 16));
 }
 
 void ensure_pack_pool(cas_ctx* ctx) {
@@ -797,27 +798,27 @@ void hex_name(char* dst, const uint8_t* digest) {
     dst[64] = 0;
 }
 
-// Gives `tmp` its final name unless that name is taken: 0 = renamed, 1 = an object with this
-// id was there already (tmp removed), < 0 = error (tmp removed).  Never replaces a file, so a
+// Gives `tmp` its final name unless that name is taken: 0 = done, 1 = an object with this id
+// was there already (tmp removed), < 0 = error (tmp removed).  Never replaces a file, so a
 // reader holding the existing object open is not disturbed, and the final name only ever
-// appears complete (rename is atomic).
-int rename_noreplace(const char* tmp, const char* target) {
+// appears complete.  A hard link plus unlink is tried first: unlike a rename between two
+// directories it does not take the file system's rename lock, so many threads can publish
+// at once; rename (without replacement) is the fallback for file systems without links.
+int publish_one(const char* tmp, const char* target) {
+    if (link(tmp, target) == 0) { unlink(tmp); return CAS_STORED_NEW; }
+    if (errno == EEXIST) { unlink(tmp); return CAS_STORED_EXISTED; }
 #if defined(SYS_renameat2)
     if (syscall(SYS_renameat2, AT_FDCWD, tmp, AT_FDCWD, target, 1u /* RENAME_NOREPLACE */) == 0) return CAS_STORED_NEW;
     if (errno == EEXIST) { unlink(tmp); return CAS_STORED_EXISTED; }
-    if (errno != EINVAL && errno != ENOSYS) { unlink(tmp); return CAS_E_IO; }
 #endif
-    if (link(tmp, target) == 0) { unlink(tmp); return CAS_STORED_NEW; }  // file systems without RENAME_NOREPLACE
-    const int err = errno;
     unlink(tmp);
-    return err == EEXIST ? CAS_STORED_EXISTED : CAS_E_IO;
+    return CAS_E_IO;
 }
 
-// Final names for a batch: tmp files made by cas_store_host (paths == NULL: writer[i] says
-// which thread's directory holds object i) or the caller's spool files.  Objects whose status
-// is already negative are skipped (their tmp file is removed if it is ours).
-void publish_tmp_files(cas_ctx* ctx, const std::string& root, uint64_t token, const uint16_t* writer,
-                       const char* const* paths, uint64_t n, const uint8_t* digests, int32_t* status) {
+// Final names for the caller's spool files (cas_publish_files).  Files whose status is already
+// negative are skipped.
+void publish_paths(cas_ctx* ctx, const std::string& root, const char* const* paths, uint64_t n, const uint8_t* digests,
+                   int32_t* status) {
     std::atomic<uint64_t> next{0};
     const std::function<void(int)> job = [&](int) {
         char hex[65];
@@ -825,37 +826,13 @@ void publish_tmp_files(cas_ctx* ctx, const std::string& root, uint64_t token, co
             const uint64_t i0 = next.fetch_add(16, std::memory_order_relaxed);
             if (i0 >= n) return;
             for (uint64_t i = i0; i < std::min(n, i0 + 16); ++i) {
-                const std::string tmp = paths ? std::string(paths[i]) : tmp_path(root, token, writer[i], i);
-                if (status[i] < 0) {
-                    if (!paths) unlink(tmp.c_str());
-                    continue;
-                }
+                if (status[i] < 0) continue;
                 hex_name(hex, digests + 32 * i);
-                status[i] = rename_noreplace(tmp.c_str(), (root + "/" + hex).c_str());
+                status[i] = publish_one(paths[i], (root + "/" + hex).c_str());
             }
         }
     };
     ctx->io_pool->run(job);
-}
-
-// Removes what is left of a store call's temporary directories (all of it after a failed call).
-void remove_tmp_dirs(cas_ctx* ctx, const std::string& root, uint64_t token, const uint16_t* writer, uint64_t n, bool files_too) {
-    if (files_too) {
-        std::atomic<uint64_t> next{0};
-        const std::function<void(int)> job = [&](int) {
-            for (;;) {
-                const uint64_t i = next.fetch_add(1, std::memory_order_relaxed);
-                if (i >= n) return;
-                if (writer[i] != 0xFFFF) unlink(tmp_path(root, token, writer[i], i).c_str());
-            }
-        };
-        ctx->io_pool->run(job);
-    }
-    char name[64];
-    for (int t = 0; t < ctx->io_pool->size(); ++t) {
-        tmp_dir_name(name, sizeof name, token, (unsigned)t);
-        rmdir((root + "/" + name).c_str());  // absent if that thread wrote nothing
-    }
 }
 
 // Sizes of n files, looked up by the pack pool's threads.  With status == NULL a file that is
@@ -1182,37 +1159,50 @@ int cas_store_host(cas_ctx* ctx, const char* dir, const void* base, const uint64
     const std::string root(dir);
     const uint64_t token = fresh_token();
 
-    // File writers run while this thread drives the GPU pipeline over the same bytes.
-    std::vector<uint16_t> writer(n, 0xFFFF);
+    // File writers run while this thread drives the GPU pipeline over the same bytes.  A writer
+    // publishes its own files: at once for files written after the digests have arrived, in
+    // one sweep for those written before (so there is no separate rename phase at the end).
     std::atomic<uint64_t> next{0};
+    std::atomic<int> outcome{0};  // 0 = still hashing, 1 = digests are in out32n, 2 = hashing failed
+    const uint8_t* digests = static_cast<const uint8_t*>(out32n);
     const std::function<void(int)> write_all = [&](int t) {
         bool have_dir = false;
-        char name[64];
+        char name[64], hex[65];
+        std::vector<uint64_t> waiting;  // written, not yet published
+        auto publish = [&](uint64_t i) {
+            hex_name(hex, digests + 32 * i);
+            status[i] = publish_one(tmp_path(root, token, (unsigned)t, i).c_str(), (root + "/" + hex).c_str());
+        };
         for (;;) {
             const uint64_t i = next.fetch_add(1, std::memory_order_relaxed);
-            if (i >= n) return;
+            if (i >= n) break;
             if (!have_dir) {
                 tmp_dir_name(name, sizeof name, token, (unsigned)t);
                 have_dir = mkdir((root + "/" + name).c_str(), 0777) == 0 || errno == EEXIST;
             }
-            writer[i] = (uint16_t)t;
-            if (!have_dir || !write_whole_file(tmp_path(root, token, (unsigned)t, i).c_str(), hbase + off[i], len[i]))
+            if (!have_dir || !write_whole_file(tmp_path(root, token, (unsigned)t, i).c_str(), hbase + off[i], len[i])) {
                 status[i] = CAS_E_IO;
+                continue;
+            }
+            if (outcome.load(std::memory_order_acquire) == 1) publish(i);
+            else waiting.push_back(i);
         }
+        int how;
+        while ((how = outcome.load(std::memory_order_acquire)) == 0) std::this_thread::sleep_for(std::chrono::microseconds(50));
+        for (uint64_t i : waiting) {
+            if (how == 1) publish(i);
+            else unlink(tmp_path(root, token, (unsigned)t, i).c_str());  // no ids: nothing may appear under a final name
+        }
+        if (have_dir) rmdir((root + "/" + name).c_str());
     };
     ctx->io_pool->start(write_all);
     ByteSource src;
     src.hbase = hbase;
     src.off = off;
     const int rc = hash_host_impl(ctx, src, len, n, static_cast<uint8_t*>(out32n));
+    outcome.store(rc ? 2 : 1, std::memory_order_release);
     ctx->io_pool->wait();
-    if (rc) {  // no ids: nothing may appear under a final name
-        remove_tmp_dirs(ctx, root, token, writer.data(), n, true);
-        return rc;
-    }
-    publish_tmp_files(ctx, root, token, writer.data(), nullptr, n, static_cast<const uint8_t*>(out32n), status);
-    remove_tmp_dirs(ctx, root, token, writer.data(), n, false);
-    return CAS_OK;
+    return rc;
 }
 
 int cas_publish_files(cas_ctx* ctx, const char* dir, const char* const* paths, uint64_t n, void* out32n,
@@ -1236,7 +1226,7 @@ int cas_publish_files(cas_ctx* ctx, const char* dir, const char* const* paths, u
     uint8_t* out = static_cast<uint8_t*>(out32n);
     for (uint64_t i = 0; i < n; ++i)
         if (status_out[i] < 0) memset(out + 32 * i, 0, 32);  // never a digest of bytes that were not all read
-    if (dir) publish_tmp_files(ctx, std::string(dir), 0, nullptr, paths, n, out, status_out);
+    if (dir) publish_paths(ctx, std::string(dir), paths, n, out, status_out);
     return CAS_OK;
 }
 

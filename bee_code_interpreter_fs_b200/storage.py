@@ -448,9 +448,11 @@ class Storage:
             if not os.path.isdir(root):
                 return {}
             if hasattr(self._hasher, "verify_names"):  # the engine tells files from other entries itself
-                names = sorted(n for n in os.listdir(root) if not n.startswith("."))
-                ok = self._hasher.verify_names(root, names)
-                return {n: bool(v == 1) for n, v in zip(names, ok.tolist()) if v != 2}
+                names = [n for n in os.listdir(root) if not n.startswith(".")]
+                ok = self._hasher.verify_names(root, names).tolist()
+                if 2 in ok:  # sub-directories and the like are not objects
+                    return {n: v == 1 for n, v in zip(names, ok) if v != 2}
+                return dict(zip(names, map(bool, ok)))
             names = sorted(e.name for e in os.scandir(root) if not e.name.startswith(".") and e.is_file())
             return self._verify_sync(names)
 

@@ -115,12 +115,13 @@ int cas_reserve(cas_ctx* ctx, uint64_t batch_bytes, uint64_t max_objects);
  * Storage.write for a batch (storage.py:44-63: open "<dir>/<id>", write, close), with
  * content-derived ids: hashes the n host objects exactly as cas_hash_host does and, while the
  * GPU pipeline runs, writes each object to a temporary file under "<dir>/.tmp-<token>.<thread>/"
- * from a few host threads; once the digests are back every temporary file is renamed to
- * "<dir>/<64 hex digits>", or removed if an object of that id exists already.  A final name only ever appears complete
- * (rename), an existing object is never replaced, and a failed call leaves no temporary file
- * behind.  `dir` is created if missing.  status_out (may be NULL) receives CAS_STORED_NEW,
- * CAS_STORED_EXISTED or CAS_E_IO per object; an object that could not be written does not
- * fail the call, its id is still returned.  No fsync, as in the reference.
+ * from several host threads; as soon as the digests are back every temporary file is given its
+ * final name "<dir>/<64 hex digits>" (hard link, then the temporary name is dropped), or just
+ * removed if an object of that id exists already.  A final name only ever appears complete, an
+ * existing object is never replaced, and a failed call leaves no temporary file behind.  `dir`
+ * is created if missing.  status_out (may be NULL) receives CAS_STORED_NEW, CAS_STORED_EXISTED
+ * or CAS_E_IO per object; an object that could not be written does not fail the call, its id is
+ * still returned.  No fsync, as in the reference.
  */
 int cas_store_host(cas_ctx* ctx, const char* dir, const void* base, const uint64_t* off, const uint64_t* len,
                    uint64_t n, void* out32n, int32_t* status_out);
@@ -128,7 +129,7 @@ int cas_store_host(cas_ctx* ctx, const char* dir, const void* base, const uint64
 /*
  * The close of Storage.writer for a batch (storage.py:44-55 plus the executor's download leg,
  * services/kubernetes_code_executor.py:138-146): hashes n spooled files as cas_hash_files does
- * and renames each to "<dir>/<id>" (or removes it if that id exists).  Unlike cas_hash_files,
+ * and gives each its final name "<dir>/<id>" (or removes it if that id exists).  Unlike cas_hash_files,
  * a file that is missing, not regular or shrinks while it is read fails only itself:
  * status_out[i] = CAS_E_IO, its digest slot is zeroed, and the other files are still hashed
  * and published.  With dir == NULL nothing is renamed (hash only, per-file status).
