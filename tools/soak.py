@@ -9,6 +9,7 @@ import argparse
 import hashlib
 import json
 import os
+import shutil
 import sys
 import tempfile
 import time
@@ -61,7 +62,13 @@ def main():
             h.set_option(_ffi.OPT_KERNEL, int(rng.integers(0, 3)))
             h.set_option(_ffi.OPT_FMA_LEVEL, int(rng.choice([0, 1, 2, 3, 3, 3, 4])))
             h.set_option(_ffi.OPT_CTAS_PER_SM, int(rng.choice([0, 0, 2, 3, 4])))
-            h.set_option(_ffi.OPT_LONG_MAX_OBJECTS, int(rng.choice([0, 592, 592, 100000])))
+            h.set_option(_ffi.OPT_LONG_MAX_OBJECTS, int(rng.choice([0, 1, 8, 592, 592, 100000])))
+            h.set_option(_ffi.OPT_LONG_MAX_PER_WARP, int(rng.choice([1, 2, 4, 8, 16, 32, 32])))
+            h.set_option(_ffi.OPT_LONG_MIN_BYTES, int(rng.choice([64, 4096, 32768])))
+            h.set_option(_ffi.OPT_FIRST_CHUNK_BYTES, int(rng.choice([65536, 1 << 20, 2 << 20, 16 << 20])))
+            h.set_option(_ffi.OPT_CHUNK_DIVISOR, int(rng.choice([1, 8, 16, 64])))
+            h.set_option(_ffi.OPT_PACK_THREADS, int(rng.choice([1, 3, 8, 12])))
+            h.set_option(_ffi.OPT_IO_THREADS, int(rng.choice([1, 5, 12, 16])))
             n = int(rng.choice([1, 2, 7, 33, 200, 1000, 5000]))
             lengths = random_lengths(rng, n).astype(np.int64)
             total = int(lengths.sum())
@@ -73,7 +80,7 @@ def main():
             blobs = [data[int(o):int(o) + int(k)].tobytes() for o, k in zip(off, lengths)]
             want = want_hex(blobs)
             scenario = ["bytes", "packed_pageable", "packed_pinned", "device", "device_order", "device_warp",
-                        "uniform", "files", "static"][int(rng.integers(0, 9))]
+                        "uniform", "files", "static", "store", "publish", "stream"][int(rng.integers(0, 12))]
             if scenario == "bytes":
                 got = h.hash_many(blobs)
             elif scenario == "packed_pageable":
@@ -109,6 +116,49 @@ def main():
                         f.write(blobs[i])
                     paths.append(p)
                 got, want = h.hash_files(paths), want[:m]
+            elif scenario == "store":
+                m = min(n, 400)
+                root = os.path.join(tmp, f"store{it}")
+                got, status = h.store_many(root, blobs[:m])
+                want = want[:m]
+                assert all(s in (0, 1) for s in status.tolist()) and sorted(os.listdir(root)) == sorted(set(want))
+                for name in list(set(want))[:20]:
+                    with open(os.path.join(root, name), "rb") as f:
+                        assert hashlib.sha256(f.read()).hexdigest() == name
+                assert h.verify_names(root, got).tolist() == [1] * m
+                shutil.rmtree(root)
+            elif scenario == "publish":
+                m = min(n, 300)
+                root, spool = os.path.join(tmp, f"pub{it}"), os.path.join(tmp, f"spool{it}")
+                os.makedirs(spool)
+                paths = []
+                for i in range(m):
+                    paths.append(os.path.join(spool, f".tmp-{i}"))
+                    with open(paths[-1], "wb") as f:
+                        f.write(blobs[i])
+                missing = int(rng.integers(0, m)) if m > 1 and rng.integers(0, 2) else -1
+                if missing >= 0:
+                    os.unlink(paths[missing])
+                got, _, status = h.publish_files(root, paths)
+                want = want[:m]
+                if missing >= 0:
+                    assert status[missing] < 0
+                    got[missing] = want[missing]
+                live = {w for i, w in enumerate(want) if i != missing}
+                assert sorted(os.listdir(root)) == sorted(live) and os.listdir(spool) == []
+                shutil.rmtree(root)
+                shutil.rmtree(spool)
+            elif scenario == "stream":
+                m = min(n, 200)
+                states = [h.stream_begin() for _ in range(m)]
+                pos = [0] * m
+                while any(pos[i] < len(blobs[i]) for i in range(m)):
+                    step = int(rng.choice([1, 63, 64, 65, 1000, 100000, 1 << 22]))
+                    pieces = [blobs[i][pos[i]:pos[i] + step] for i in range(m)]
+                    for i in range(m):
+                        pos[i] += len(pieces[i])
+                    h.stream_update(states, pieces)
+                got, want = h.stream_finish(states), want[:m]
             else:  # static
                 keep, used = [], 0
                 for b in blobs[:STATIC_MAX_OBJECTS]:
