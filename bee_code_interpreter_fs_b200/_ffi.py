@@ -17,7 +17,7 @@ STORED_NEW, STORED_EXISTED = 0, 1
 SYMBOLS = (
     "cas_create", "cas_destroy", "cas_last_error", "cas_set_option", "cas_get_option", "cas_device_info",
     "cas_hash_host", "cas_hash_files", "cas_hash_device", "cas_hash_device_long", "cas_hash_device_uniform", "cas_gen_synthetic", "cas_int32_peak",
-    "cas_launch_count", "cas_version", "cas_hash_host_static", "cas_reserve", "cas_store_host", "cas_publish_files", "cas_verify_names", "cas_stream_begin", "cas_stream_update", "cas_stream_finish",
+    "cas_launch_count", "cas_version", "cas_hash_host_static", "cas_reserve", "cas_store_host", "cas_publish_files", "cas_verify_names", "cas_stream_begin", "cas_stream_update", "cas_stream_finish", "cas_set_h2d_gate",
 )
 STATIC_MAX_OBJECTS = 1024
 STATIC_MAX_BYTES = 8 << 20
@@ -93,6 +93,8 @@ def load() -> ctypes.CDLL:
     lib.cas_stream_update.restype = ci
     lib.cas_stream_finish.argtypes = [vp, vp, u64, vp]
     lib.cas_stream_finish.restype = ci
+    lib.cas_set_h2d_gate.argtypes = [vp, ctypes.c_char_p, ci]
+    lib.cas_set_h2d_gate.restype = ci
     lib.cas_launch_count.argtypes = [vp]
     lib.cas_launch_count.restype = u64
     lib.cas_version.argtypes = []

@@ -16,6 +16,7 @@
 #include <cuda_runtime.h>
 #include <errno.h>
 #include <fcntl.h>
+#include <semaphore.h>
 #include <sys/stat.h>
 #include <sys/syscall.h>
 #include <sys/time.h>
@@ -158,6 +159,9 @@ struct cas_ctx {
     PackPool* io_pool = nullptr;  // file writers of cas_store_host (they run while the pack pool feeds the GPU)
     int io_threads = 0;
     bool trace = false;           // B200CAS_TRACE=1: one line of host-pipeline timings per call on stderr
+    sem_t* gate = SEM_FAILED;     // optional cross-process limit on concurrent host->device copy chunks (cas_set_h2d_gate)
+    std::string gate_name;
+    uint64_t gate_timeouts = 0;
     uint32_t* d_sink = nullptr;
     bool host_path_dirty = false;  // set while a host-path call is in progress; stays set if it failed
 };
@@ -496,6 +500,7 @@ void cas_destroy(cas_ctx* ctx) {
         if (st) cudaStreamDestroy(st);
     if (ctx->s_copy) cudaStreamDestroy(ctx->s_copy);
     if (ctx->d_sink) cudaFree(ctx->d_sink);
+    if (ctx->gate != SEM_FAILED) sem_close(ctx->gate);
     delete ctx->pool;
     delete ctx->io_pool;
     delete ctx;
@@ -868,6 +873,24 @@ int stat_files(cas_ctx* ctx, const char* const* paths, uint64_t n, uint64_t* len
     return CAS_OK;
 }
 
+// Host->device gate: a named POSIX semaphore shared by the processes (or contexts) that copy
+// through the same host uplink.  A chunk's copies are enqueued only while a slot is held; the
+// slot is given back by a host function that runs in the copy stream right after them.
+bool gate_acquire(cas_ctx* ctx) {
+    if (ctx->gate == SEM_FAILED) return false;
+    timespec ts;
+    clock_gettime(CLOCK_REALTIME, &ts);
+    ts.tv_sec += 1;  // never wait for ever on a slot somebody may have died with
+    for (;;) {
+        if (sem_timedwait(ctx->gate, &ts) == 0) return true;
+        if (errno == EINTR) continue;
+        ++ctx->gate_timeouts;
+        return false;
+    }
+}
+
+void CUDART_CB gate_release(void* sem) { sem_post(static_cast<sem_t*>(sem)); }
+
 double now_s() {
     return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }
@@ -997,8 +1020,14 @@ int hash_host_impl(cas_ctx* ctx, const ByteSource& srcs, const uint64_t* len, ui
             }
             if (c1 > c0) {
                 if (pinned_src && pieces.size() <= 64) {
+                    const bool held = gate_acquire(ctx);
+                    cudaError_t ce = cudaSuccess;
                     for (auto& pc : pieces)
-                        CU(cudaMemcpyAsync(d_base + pc.dst, pc.src, pc.bytes, cudaMemcpyHostToDevice, ctx->s_copy));
+                        if (ce == cudaSuccess)
+                            ce = cudaMemcpyAsync(d_base + pc.dst, pc.src, pc.bytes, cudaMemcpyHostToDevice, ctx->s_copy);
+                    if (held && (ce != cudaSuccess || cudaLaunchHostFunc(ctx->s_copy, gate_release, ctx->gate) != cudaSuccess))
+                        sem_post(ctx->gate);  // the slot must not be lost with the failed call
+                    if (ce != cudaSuccess) return fail(ctx, CAS_E_CUDA, "host->device copy of a chunk", ce);
                 } else if (!pieces.empty()) {
                     const double tw0 = ctx->trace ? now_s() : 0.0;
                     if (sg.used) CU(cudaEventSynchronize(sg.ev));  // its previous H2D has left the staging
@@ -1129,6 +1158,22 @@ int cas_hash_files(cas_ctx* ctx, const char* const* paths, uint64_t n, void* out
     ByteSource src;
     src.paths = paths;
     return hash_host_impl(ctx, src, len.data(), n, static_cast<uint8_t*>(out32n));
+}
+
+int cas_set_h2d_gate(cas_ctx* ctx, const char* name, int slots) {
+    if (!ctx) return CAS_E_ARG;
+    if (ctx->gate != SEM_FAILED) {
+        sem_close(ctx->gate);
+        ctx->gate = SEM_FAILED;
+        ctx->gate_name.clear();
+    }
+    if (!name) return CAS_OK;
+    if (name[0] != '/' || slots < 1) return fail(ctx, CAS_E_ARG, "cas_set_h2d_gate: name must start with '/' and slots be >= 1");
+    sem_t* s = sem_open(name, O_CREAT, 0600, (unsigned)slots);
+    if (s == SEM_FAILED) return fail(ctx, CAS_E_IO, "cas_set_h2d_gate: sem_open failed");
+    ctx->gate = s;
+    ctx->gate_name = name;
+    return CAS_OK;
 }
 
 int cas_reserve(cas_ctx* ctx, uint64_t batch_bytes, uint64_t max_objects) {

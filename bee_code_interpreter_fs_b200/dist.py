@@ -43,6 +43,37 @@ def gpu_order(device_count: int) -> list[int]:
     return order
 
 
+def h2d_gate_for(device: int, device_count: int) -> tuple[str, int] | None:
+    """(gate name, slots) for the host->device gate of ``device``'s uplink group, or None.
+
+    Ranks of one torchrun launch (same parent process) whose GPUs hang off the same group of the
+    measured map share a gate, so that no more than ``gate_slots_per_group`` of them copy from
+    host memory at the same time (GpuHasher.set_h2d_gate).  Only meaningful when more ranks than
+    slots share a group."""
+    try:
+        import json
+
+        with open(_ORDER_FILE) as f:
+            info = json.load(f)
+        groups, slots = info["uplink_groups"], int(info["gate_slots_per_group"])
+        if sorted(g for grp in groups for g in grp) != list(range(device_count)):
+            return None
+        for k, grp in enumerate(groups):
+            if device in grp:
+                return f"/b200cas-h2d-{os.getppid()}-g{k}", slots
+    except (OSError, ValueError, KeyError):
+        pass
+    return None
+
+
+def remove_h2d_gate(name: str) -> None:
+    """sem_unlink for a gate name (Linux keeps named semaphores as /dev/shm/sem.<name>)."""
+    try:
+        os.unlink("/dev/shm/sem." + name.lstrip("/"))
+    except OSError:
+        pass
+
+
 def gpu_for_rank(local_rank: int, device_count: int) -> int:
     order = gpu_order(device_count)
     return order[local_rank] if local_rank < len(order) else local_rank

@@ -193,6 +193,12 @@ class GpuHasher:
         with self._lock:
             self._check(self._lib.cas_reserve(self._ctx, int(batch_bytes), int(max_objects)))
 
+    def set_h2d_gate(self, name: str | None, slots: int = 2) -> None:
+        """Take turns with the other hashers (any process) that name the same gate when copying
+        from pinned host memory: at most ``slots`` copy chunks run at once (cas_set_h2d_gate)."""
+        with self._lock:
+            self._check(self._lib.cas_set_h2d_gate(self._ctx, None if name is None else name.encode(), int(slots)))
+
     # -- hashing and storing in one call (the Storage-shaped path) ----------------------------
     def store_many(self, root: str | os.PathLike, objs: Sequence[BytesLike]) -> tuple[list[str], np.ndarray]:
         """Hash a batch and store every object as ``<root>/<id>`` (cas_store_host: file writers run

@@ -269,6 +269,11 @@ def run_ours(args) -> None:
     for key, val in ((_ffi.OPT_KERNEL, args.kernel), (_ffi.OPT_FMA_LEVEL, args.fma), (_ffi.OPT_CTAS_PER_SM, args.ctas)):
         if val is not None:
             h.set_option(key, val)
+    gate = None
+    if world > 1 and args.h2d_gate == "on":
+        gate = cdist.h2d_gate_for(local_rank, torch.cuda.device_count())
+        if gate:
+            h.set_h2d_gate(*gate)
     n, length = args.objects, args.object_bytes
     first_obj = rank * n
     total_bytes = n * length
@@ -448,6 +453,9 @@ def run_ours(args) -> None:
                "single_thread_gb_s": one, "c_port_all_cores_gb_s": port_rate}
         log(f"[cpu] hashlib {cores} threads {rate:.2f} GB/s, 1 thread {one:.2f} GB/s, C port {port_rate:.2f} GB/s")
 
+    if gate:
+        cdist.barrier()
+        cdist.remove_h2d_gate(gate[0])
     if rank != 0:
         return
     per_launch_ms = ms / args.steps
@@ -496,6 +504,7 @@ def run_ours(args) -> None:
                 "d2h_bytes_per_step": n * 32, "steps": e2e_steps, "host_buffer_bytes": host_objects * length,
                 "calls_per_step": passes, "timing": "host wall clock around synchronous cas_hash_host calls, max over ranks",
                 "pinned_h2d_probe_gb_s_per_gpu": h2d_gbs, "numa": numa,
+                "h2d_gate": {"name": gate[0], "slots": gate[1]} if gate else None,
                 "note": "bounded by host->device copies: compare value / n_gpus with the plain-memcpy probe"},
         "gpu_launches": int(timed_launches), "gpu_launches_e2e": int(e2e_launches),
         "verified": f"{len(sample_idx)} sampled kernel-only digests bit-exact vs hashlib; all {e2e_checked} end-to-end "
@@ -529,6 +538,8 @@ def main() -> None:
     ap.add_argument("--ref-sample-bytes", type=float, default=0.0, help="reference arm: bytes per step (0 = as much of the config as --ref-seconds allows)")
     ap.add_argument("--ref-seconds", type=float, default=125.0, help="reference arm: time budget for all its steps")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--h2d-gate", choices=("on", "off"), default="off",
+                    help="N > 1: ranks behind the same host uplink take turns copying (measured map in profiles/)")
     args = ap.parse_args()
     capture_stdout()
     if args.warmup < 3 and args.impl == "ours":

@@ -107,6 +107,18 @@ int cas_hash_files(cas_ctx* ctx, const char* const* paths, uint64_t n, void* out
  */
 int cas_reserve(cas_ctx* ctx, uint64_t batch_bytes, uint64_t max_objects);
 
+/*
+ * Optional limit on how many host->device copy chunks run at once across the contexts and
+ * processes that name the same gate (a POSIX named semaphore, created with `slots` if it does
+ * not exist; name must start with '/').  On a host whose aggregate host->device bandwidth
+ * drops when every GPU copies at the same time (profiles/r02_h2d_matrix.jsonl: 220 GB/s with
+ * four B200s copying, 186 GB/s with eight) the ranks that share an uplink take turns instead.
+ * Applies to cas_hash_host's direct copies from page-locked memory; a slot is never waited for
+ * longer than a second.  name == NULL removes the gate.  Whoever created the name removes it
+ * with sem_unlink when the job is over.  No counterpart in the reference (it has no GPU path).
+ */
+int cas_set_h2d_gate(cas_ctx* ctx, const char* name, int slots);
+
 /* Per-object results of cas_store_host / cas_publish_files (status_out[i]); negative = CAS_E_* for that object. */
 #define CAS_STORED_NEW 0     /* the object now exists under its id */
 #define CAS_STORED_EXISTED 1 /* an object with this id was in the store already; it was left untouched */

@@ -279,3 +279,51 @@ def test_scrub_in_the_engine_tells_objects_from_everything_else(tmp_path, hasher
         assert await st.verify(ids[:2] + ["0" * 64]) == {ids[0]: True, ids[1]: True, "0" * 64: False}
 
     asyncio.run(go())
+
+
+def test_h2d_gate_lets_contexts_take_turns_and_changes_no_digest(hasher):
+    """cas_set_h2d_gate: two contexts that name the same one-slot gate copy their chunks in turn;
+    the digests are the same, the slot always comes back (the second round would otherwise crawl
+    along on one-second time-outs), and removing the gate restores the ungated path."""
+    import threading
+    import time
+
+    import numpy as np
+    import torch
+
+    from bee_code_interpreter_fs_b200 import GpuHasher, dist as cdist
+
+    name = f"/b200cas-test-gate-{os.getpid()}"
+    n, length = 3000, 65536
+    host = torch.empty(n * length, dtype=torch.uint8).pin_memory()
+    host.numpy()[:] = np.random.default_rng(8).integers(0, 256, size=n * length, dtype=np.uint8)
+    off = np.arange(n, dtype=np.uint64) * length
+    lens = np.full(n, length, dtype=np.uint64)
+    want = hasher.digest_packed(host, off, lens)
+    assert bytes(want[7]) == hashlib.sha256(host.numpy()[7 * length:8 * length]).digest()
+    got, errors = [None, None], []
+
+    def run(k):
+        try:
+            with GpuHasher(0) as h:
+                h.set_option(3, 16 << 20)  # CAS_OPT_WAVE_BYTES: a dozen gated chunks per call
+                h.set_h2d_gate(name, 1)
+                for _ in range(3):
+                    got[k] = h.digest_packed(host, off, lens)
+                h.set_h2d_gate(None)
+                got[k] = h.digest_packed(host, off, lens)
+        except Exception as e:  # noqa: BLE001
+            errors.append(e)
+
+    try:
+        t0 = time.perf_counter()
+        threads = [threading.Thread(target=run, args=(k,)) for k in range(2)]
+        for t in threads:
+            t.start()
+        for t in threads:
+            t.join()
+        assert not errors, errors
+        assert (got[0] == want).all() and (got[1] == want).all()
+        assert time.perf_counter() - t0 < 10.0  # no slot was lost: nothing waited out a time-out
+    finally:
+        cdist.remove_h2d_gate(name)
