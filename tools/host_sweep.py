@@ -34,9 +34,9 @@ def main():
     objs = [blob[i * length:(i + 1) * length].tobytes() for i in range(10000)]
     for n in (10000, 4096):
         sub = objs[:n]
-        for pack in (6, 8, 12, 16):
+        for pack in (8, 12, 16):
             for div in (8, 16):
-                for first in (1, 2, 4):
+                for first in (2,):
                     h.set_option(_ffi.OPT_PACK_THREADS, pack)
                     h.set_option(_ffi.OPT_CHUNK_DIVISOR, div)
                     h.set_option(_ffi.OPT_FIRST_CHUNK_BYTES, first << 20)
@@ -49,7 +49,7 @@ def main():
     h.set_option(_ffi.OPT_FIRST_CHUNK_BYTES, 2 << 20)
     base = tempfile.mkdtemp(prefix="b200cas-sweep-", dir="/dev/shm" if os.path.isdir("/dev/shm") else None)
     try:
-        for io in (4, 8, 12, 16, 24, 32):
+        for io in (4, 8, 12, 16):
             h.set_option(_ffi.OPT_IO_THREADS, io)
             root = os.path.join(base, f"s{io}")
             t0 = time.perf_counter()
