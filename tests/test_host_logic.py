@@ -326,3 +326,48 @@ def test_engine_failure_reaches_the_caller(tmp_path):
 
     run(go())
     assert os.listdir(tmp_path) == []
+
+
+# ------------------------------------------------- rank -> GPU order, gate names, addresses --
+def test_gpu_order_uses_the_measured_map_only_when_it_fits_the_node(monkeypatch):
+    from bee_code_interpreter_fs_b200 import dist as cdist
+
+    monkeypatch.delenv("B200CAS_GPU_ORDER", raising=False)
+    order = cdist.gpu_order(8)  # the committed map was measured on an 8-GPU node
+    assert sorted(order) == list(range(8))
+    assert {g // 4 for g in order[:2]} == {0, 1} and {g // 4 for g in order[:4]} == {0, 1}  # both uplink halves early
+    assert cdist.gpu_order(4) == [0, 1, 2, 3] and cdist.gpu_order(1) == [0]  # another node shape: identity
+    monkeypatch.setenv("B200CAS_GPU_ORDER", "3,2,1,0")
+    assert cdist.gpu_order(4) == [3, 2, 1, 0] and cdist.gpu_for_rank(1, 4) == 2
+    assert cdist.gpu_order(8) == list(range(8))  # an override that does not name every GPU is ignored
+    monkeypatch.setenv("B200CAS_GPU_ORDER", "nonsense")
+    assert cdist.gpu_order(2) == [0, 1]
+
+
+def test_gate_names_group_ranks_by_uplink_and_by_launch():
+    from bee_code_interpreter_fs_b200 import dist as cdist
+
+    a, b, c = cdist.h2d_gate_for(0, 8), cdist.h2d_gate_for(3, 8), cdist.h2d_gate_for(5, 8)
+    assert a == b and a != c and a[1] == c[1] == 2
+    assert a[0].startswith("/b200cas-h2d-") and str(os.getppid()) in a[0]
+    assert cdist.h2d_gate_for(0, 4) is None  # the map describes another node shape
+    cdist.remove_h2d_gate("/b200cas-h2d-does-not-exist")  # never raises
+
+
+def test_addresses_of_bytes_objects_match_ctypes():
+    import ctypes
+
+    import numpy as np
+
+    from bee_code_interpreter_fs_b200 import hasher
+
+    objs = [b"", b"a", os.urandom(100), os.urandom(70000), b"x" * 4096]
+    addr, length, keep = hasher._addresses(objs)
+    assert length.tolist() == [len(o) for o in objs]
+    for a, o in zip(addr.tolist(), objs):
+        assert ctypes.string_at(a, len(o)) == o
+    if hasher._BYTES_DATA_OFFSET:
+        want = np.frombuffer((ctypes.c_char_p * len(objs))(*objs), dtype=np.uint64, count=len(objs))
+        assert (addr == want).all()
+    mixed, mlen, _ = hasher._addresses([bytearray(b"abc"), memoryview(b"defg"), np.arange(5, dtype=np.uint8)])
+    assert mlen.tolist() == [3, 4, 5] and ctypes.string_at(int(mixed[1]), 4) == b"defg"
