@@ -767,7 +767,7 @@ uint64_t fresh_token() {
 
 // Temporary files live in per-writer-thread directories "<dir>/.tmp-<token>.<t>/": creating a
 // file takes its parent directory's lock, and with one directory per thread the writers do
-// not queue on it (nor on the store directory, which then only sees the final renames).
+// not queue on it (nor on the store directory, which then only sees the final links).
 // The names start with '.', which no object id can (the reference's Hash pattern,
 // utils/validation.py:19), so a reader can never mistake anything in there for an object.
 void tmp_dir_name(char* dst, size_t cap, uint64_t token, unsigned writer) {
@@ -804,19 +804,20 @@ void hex_name(char* dst, const uint8_t* digest) {
 }
 
 // Gives `tmp` its final name unless that name is taken: 0 = done, 1 = an object with this id
-// was there already (tmp removed), < 0 = error (tmp removed).  Never replaces a file, so a
-// reader holding the existing object open is not disturbed, and the final name only ever
-// appears complete.  A hard link plus unlink is tried first: unlike a rename between two
-// directories it does not take the file system's rename lock, so many threads can publish
-// at once; rename (without replacement) is the fallback for file systems without links.
-int publish_one(const char* tmp, const char* target) {
+// was there already (tmp removed), < 0 = error.  Never replaces a file, so a reader holding
+// the existing object open is not disturbed, and the final name only ever appears complete.
+// A hard link plus unlink is tried first: unlike a rename between two directories it does not
+// take the file system's rename lock, so many threads can publish at once; rename (without
+// replacement) is the fallback for file systems without links.  On an error the temporary file
+// is removed if it is one of ours; a caller's spool file is left for the caller to deal with.
+int publish_one(const char* tmp, const char* target, bool ours) {
     if (link(tmp, target) == 0) { unlink(tmp); return CAS_STORED_NEW; }
     if (errno == EEXIST) { unlink(tmp); return CAS_STORED_EXISTED; }
 #if defined(SYS_renameat2)
     if (syscall(SYS_renameat2, AT_FDCWD, tmp, AT_FDCWD, target, 1u /* RENAME_NOREPLACE */) == 0) return CAS_STORED_NEW;
     if (errno == EEXIST) { unlink(tmp); return CAS_STORED_EXISTED; }
 #endif
-    unlink(tmp);
+    if (ours) unlink(tmp);
     return CAS_E_IO;
 }
 
@@ -833,7 +834,7 @@ void publish_paths(cas_ctx* ctx, const std::string& root, const char* const* pat
             for (uint64_t i = i0; i < std::min(n, i0 + 16); ++i) {
                 if (status[i] < 0) continue;
                 hex_name(hex, digests + 32 * i);
-                status[i] = publish_one(paths[i], (root + "/" + hex).c_str());
+                status[i] = publish_one(paths[i], (root + "/" + hex).c_str(), false);
             }
         }
     };
@@ -1163,6 +1164,7 @@ int cas_hash_files(cas_ctx* ctx, const char* const* paths, uint64_t n, void* out
 int cas_set_h2d_gate(cas_ctx* ctx, const char* name, int slots) {
     if (!ctx) return CAS_E_ARG;
     if (ctx->gate != SEM_FAILED) {
+        if (ctx->s_copy) cudaStreamSynchronize(ctx->s_copy);  // a failed call may have left a release queued
         sem_close(ctx->gate);
         ctx->gate = SEM_FAILED;
         ctx->gate_name.clear();
@@ -1216,7 +1218,7 @@ int cas_store_host(cas_ctx* ctx, const char* dir, const void* base, const uint64
         std::vector<uint64_t> waiting;  // written, not yet published
         auto publish = [&](uint64_t i) {
             hex_name(hex, digests + 32 * i);
-            status[i] = publish_one(tmp_path(root, token, (unsigned)t, i).c_str(), (root + "/" + hex).c_str());
+            status[i] = publish_one(tmp_path(root, token, (unsigned)t, i).c_str(), (root + "/" + hex).c_str(), true);
         };
         for (;;) {
             const uint64_t i = next.fetch_add(1, std::memory_order_relaxed);
@@ -1347,7 +1349,12 @@ void gather2(uint8_t* dst, const uint8_t* a, uint64_t alen, const uint8_t* b, ui
 int stream_blocks(cas_ctx* ctx, cas_stream_state* const* s, const uint8_t* const* a, const uint64_t* alen,
                   const uint8_t* const* b, const uint64_t* blen, uint64_t n) {
     if (ctx->host_path_dirty) CU(cudaDeviceSynchronize());
-    const uint64_t round_cap = std::max<uint64_t>(MiB, std::min<uint64_t>(ctx->wave_bytes, 256 * MiB)) & ~63ull;
+    uint64_t total = 0;
+    for (uint64_t i = 0; i < n; ++i) total += alen[i] + blen[i];
+    if (total == 0) return CAS_OK;
+    // One staging buffer's worth per round, and no more staging than this call needs.
+    const uint64_t round_cap =
+        std::max<uint64_t>(MiB, std::min<uint64_t>({ctx->wave_bytes, 256 * MiB, (total + MiB - 1) & ~(MiB - 1)})) & ~63ull;
     int rc = ensure_host_path(ctx, round_cap, round_cap, n);
     if (rc) return rc;
     ctx->host_path_dirty = true;
