@@ -341,10 +341,12 @@ class MultiGpuHasher:
     """Shards a batch by object across several devices of one node (no collective)."""
 
     def __init__(self, devices: Sequence[int] | None = None):
-        if devices is None:
+        if devices is None:  # every visible GPU, in the measured uplink order (dist.gpu_order)
             import torch
 
-            devices = list(range(torch.cuda.device_count()))
+            from .dist import gpu_order
+
+            devices = gpu_order(torch.cuda.device_count())
         if not devices:
             raise CasError(_ffi.CAS_E_NODEVICE, "no CUDA device is visible (this engine has no CPU fallback)")
         self.hashers = [GpuHasher(d) for d in devices]
