@@ -155,10 +155,10 @@ class _SpoolWriter:
 
 
 class Storage:
-    """
-    Storage is a collection of objects. Objects consist of binary data and are identified by their SHA-256 hash.
+    """Flat store of immutable binary objects, each named by the SHA-256 of its content.
 
-    Backed by the filesystem: each object is a file named by its id under ``storage_path``.
+    One file per object under ``storage_path`` (the layout of the reference's store,
+    storage.py:53), so an unmodified reader of that directory keeps working.
     """
 
     def __init__(self, storage_path: str, hasher=None, device: int = 0, batch_window: float = 0.0,
@@ -345,11 +345,11 @@ class Storage:
     # -- the reference's interface ------------------------------------------------------------
     @asynccontextmanager
     async def writer(self) -> AsyncIterator[ObjectWriter]:
-        """
-        Async context manager for writing a new object to the storage.
+        """Streams a new object into the store (same shape as the reference's ``writer``,
+        storage.py:44-55): ``await w.write(chunk)`` inside the block, ``w.hash`` after it.
 
-        The final hash can be retrieved by using the `.hash` attribute once the
-        context has been left (the id depends on every byte written).
+        The id depends on every byte, so it exists once the block has been left -- which is
+        where the executor's download leg reads it (kubernetes_code_executor.py:146).
         """
         if not self._dir_ready:  # one hop, the first time only
             await self.storage_path.mkdir(parents=True, exist_ok=True)
@@ -373,17 +373,15 @@ class Storage:
             raise
 
     async def write(self, data: bytes) -> str:
-        """
-        Writes the data to the storage and returns the hash of the object.
-        """
+        """Stores ``data`` and returns its id (storage.py:57-63).  Calls made at the same time
+        share one engine batch."""
         return await self._batcher.submit(bytes(data), _STORE)
 
     @asynccontextmanager
     @validate_call
     async def reader(self, object_hash: Hash) -> AsyncIterator[ObjectReader]:
-        """
-        Async context manager that opens an object for reading.
-        """
+        """Opens a stored object for chunked reads (storage.py:65-75); an unknown or empty id
+        raises ``FileNotFoundError("File not found: <id>")`` as in the reference."""
         target_file = self.storage_path / object_hash
         if not object_hash or not await target_file.exists():
             raise FileNotFoundError(f"File not found: {object_hash}")
@@ -392,24 +390,19 @@ class Storage:
 
     @validate_call
     async def read(self, object_hash: Hash) -> bytes:
-        """
-        Reads the object with the given hash and returns it.
-        """
+        """The whole content of one object (storage.py:77-83)."""
         async with self.reader(object_hash) as f:
             return await f.read()
 
     @validate_call
     async def exists(self, object_hash: Hash) -> bool:
-        """
-        Check if an object with the given hash exists in the storage.
-        """
+        """Whether an object of this id is stored (storage.py:85-90)."""
         return await (self.storage_path / object_hash).exists()
 
     @validate_call
     async def delete(self, object_hash: Hash) -> None:
-        """
-        Delete an object with the given hash from the storage.
-        """
+        """Lets go of one holder of the object; the file goes with the last holder
+        (storage.py:92-101 removes it at once: there ids are unique per write)."""
         await asyncio.get_running_loop().run_in_executor(None, self._delete_sync, object_hash)
 
     # -- additive batch API ---------------------------------------------------------------------
