@@ -273,6 +273,20 @@ int launch_batch(cas_ctx* ctx, cas::BatchArgs a, cudaStream_t st) {
         ++ctx->launches;
         return CAS_OK;
     }
+    // Uniform batches of just over one wave (3 x 256-thread CTAs = 24 warps per SM): the part that
+    // does not fit would run as a nearly empty second wave (512 CTAs on 444 slots cost 1.33 waves,
+    // profiles/r02_tail_wave.jsonl).  Seven 128-thread CTAs per SM hold up to 28 warps at the same
+    // register budget, so everything up to 1.17 waves is resident at once.  The shard size of
+    // BASELINE config 3 split over eight GPUs (131 072 objects) falls in this window.
+    if (ctx->fma_level == 3 && ctx->ctas_per_sm == 0 && ctx->kernel == 2 && tma_eligible(a)) {
+        const uint64_t warps = (a.n + 31) / 32, sms = (uint64_t)ctx->sm_count;
+        if (warps > 24 * sms && warps <= 28 * sms) {
+            e = launch_one<3, 7, 128>(ctx, ctx->kernel, a, st);
+            if (e != cudaSuccess) return fail(ctx, CAS_E_CUDA, "sha256 batch kernel launch (one-wave shape)", e);
+            ++ctx->launches;
+            return CAS_OK;
+        }
+    }
     switch (ctx->fma_level) {
         case 0: e = launch_occ<0>(ctx, ctx->kernel, a, st); break;
         case 1: e = launch_occ<1>(ctx, ctx->kernel, a, st); break;

@@ -81,6 +81,22 @@ def test_uniform_device_path_matches_oracle(hasher, kernel, length, stride, n):
         assert bytes(host[stride * (n - 1): stride * (n - 1) + length]) == oracle.synth_object(0xB200, 11 + n - 1, length)
 
 
+@pytest.mark.parametrize("n", [148 * 24 * 32 + 1, 120000, 148 * 28 * 32])
+def test_one_wave_launch_shape_for_batches_just_over_a_wave(hasher, n):
+    """Uniform batches of 1.0-1.17 waves (24 to 28 warps per SM) run as seven 128-thread CTAs per SM
+    instead of three 256-thread ones; the window's edges and its middle, every digest."""
+    assert hasher.device_info()["sm_count"] == 148
+    length, stride = 100, 112
+    buf = torch.empty(n * stride, dtype=torch.uint8, device="cuda:0")
+    hasher.gen_synthetic(buf, 3, 0, n, length, stride)
+    got = hasher.digest_device_uniform(buf, stride, length, n).cpu().numpy()
+    host = buf.cpu().numpy().reshape(n, stride)[:, :length]
+    want = np.frombuffer(b"".join(hashlib.sha256(row).digest() for row in host), dtype=np.uint8).reshape(n, 32)
+    assert (got == want).all()
+    configure(hasher, ctas=3)  # the ordinary shape on the same batch
+    assert (hasher.digest_device_uniform(buf, stride, length, n).cpu().numpy() == want).all()
+
+
 @pytest.mark.parametrize("fma", FMA_LEVELS)
 def test_fma_levels_agree_on_tma_path(hasher, fma):
     configure(hasher, 2, fma)
