@@ -203,10 +203,12 @@ def run_reference(args) -> None:
     buf = np.empty(sample * length, dtype=np.uint8)
     from concurrent.futures import ThreadPoolExecutor
 
-    def fill(t):  # the C generator drops the GIL: one slice of objects per thread
+    def fill(t):  # the C generator drops the GIL: one slice of objects per thread, in bounded pieces
         lo, hi = sample * t // cores, sample * (t + 1) // cores
-        if hi > lo:
-            buf[lo * length: hi * length] = oracle.synth_batch(SEED, lo, hi - lo, length)
+        step = max(1, (64 << 20) // max(1, length))
+        for a in range(lo, hi, step):
+            b = min(hi, a + step)
+            buf[a * length: b * length] = oracle.synth_batch(SEED, a, b - a, length)
 
     with ThreadPoolExecutor(cores) as ex:
         list(ex.map(fill, range(cores)))
