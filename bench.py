@@ -538,7 +538,7 @@ def main() -> None:
     ap.add_argument("--e2e-host-bytes", type=int, default=64 << 30)
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--ref-sample-bytes", type=float, default=0.0, help="reference arm: bytes per step (0 = as much of the config as --ref-seconds allows)")
-    ap.add_argument("--ref-seconds", type=float, default=125.0, help="reference arm: time budget for all its steps")
+    ap.add_argument("--ref-seconds", type=float, default=160.0, help="reference arm: time budget for all its steps")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--h2d-gate", choices=("on", "off"), default="off",
                     help="N > 1: ranks behind the same host uplink take turns copying (measured map in profiles/)")
